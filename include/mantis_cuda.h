@@ -1,0 +1,99 @@
+/*
+ * mantis_cuda.h -- C ABI of libmantis_cuda.so: the B200 (sm_100a) implementation of
+ * mantis's per-frame localization hot path.
+ *
+ * The reference (k-sheridan/mantis) has no plugin / FFI layer: its stages are
+ * header-only free functions compiled into the ROS node.  The seam is therefore
+ * placed directly under its two entry points
+ *   - topic callback  quadDetection(ImageConstPtr, CameraInfoConstPtr)  src/mantis3.cpp:68
+ *   - service handler runMantis(Request&, Response&)                    src/mantis_server.cpp:23
+ * mantis_localize_batch() takes what those receive (images + K + D) and returns
+ * what they emit (pose, error/weight, counts; srv/mantisService.srv:1-12).  The
+ * stage-level entry points expose each reference function on the path so that
+ * tests and benchmarks can check and time it in isolation.
+ *
+ * Conventions
+ *   - every function returns MANTIS_OK (0) or a negative mantis_status; nothing
+ *     throws or exits across the ABI (the reference exit(1)s inside RPP.cpp:452).
+ *   - `mem` says where the caller's image / result buffers live: MANTIS_MEM_HOST
+ *     (the library stages them through pinned memory and copies on its stream) or
+ *     MANTIS_MEM_DEVICE (pointers are device pointers on the context's device).
+ *   - a context is bound to one device and one stream; one context per host
+ *     thread.  No allocation happens on the hot calls once the context has seen
+ *     the largest batch / frame size (scratch grows monotonically).
+ *   - all calls are synchronous with respect to the host unless stated.
+ */
+#ifndef MANTIS_CUDA_H
+#define MANTIS_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mantis_ctx mantis_ctx;
+
+typedef enum mantis_status {
+    MANTIS_OK = 0,
+    MANTIS_ERR_INVALID = -1,     /* bad argument */
+    MANTIS_ERR_CUDA = -2,        /* CUDA runtime failure; see mantis_last_error() */
+    MANTIS_ERR_NO_DEVICE = -3,   /* no CUDA device: there is no CPU fallback */
+    MANTIS_ERR_UNSUPPORTED = -4, /* frame too large for the on-chip stages */
+    MANTIS_ERR_NOMEM = -5
+} mantis_status;
+
+enum { MANTIS_MEM_HOST = 0, MANTIS_MEM_DEVICE = 1 };
+
+/* Tunables of the reference: rosparams of getParameters()
+ * (include/mantis3/Mantis3Params.h:154-194) and its compile-time defines (:12-68). */
+typedef struct mantis_config {
+    int32_t canny_hysteresis;   /* ~canny_hysteresis, default 50; Canny(T, 3T)   :162 */
+    int32_t polygon_epsilon;    /* ~polygon_epsilon, default 10                  :164 */
+    double search_radius_multiplier; /* ~neighborhood_search_radius_multiplier .1 :166 */
+    double grid_spacing;        /* ~grid_spacing, default 0.32                   :167 */
+    int32_t grid_size;          /* GRID_SIZE 9                                   :23  */
+    double quad_stretch_factor; /* QUAD_STRECH_FACTOR 1.3                        :20  */
+    double max_quad_error;      /* MAX_QUAD_ERROR 0.5                            :26  */
+    double max_angle_difference;/* MAX_ANGLE_DIFFERENCE 0.2                      :28  */
+    double projection_bias;     /* PROJECTION_BIAS 1.1                           :37  */
+    double color_projection_bias; /* COLOR_PROJECTION_BIAS 1.1                   :55  */
+    double rot_sigma;           /* ROT_SIGMA 0.03                                :62  */
+    double trans_sigma;         /* TRANS_SIGMA 0.01                              :63  */
+    int32_t particles;          /* optimizeHypothesisWithParticleFilter default 50  PoseAdjustment.h:29 */
+    int32_t iterations;         /* ... default 10 */
+    uint64_t rng_seed;          /* cv::RNG rng(1)                                :87  */
+} mantis_config;
+
+/* Fills *cfg with the reference's defaults. */
+void mantis_default_config(mantis_config* cfg);
+
+int mantis_create(const mantis_config* cfg, int device, mantis_ctx** out);
+int mantis_destroy(mantis_ctx* ctx);
+const char* mantis_strerror(int status);
+/* Text of the last CUDA error seen by this context (empty string if none). */
+const char* mantis_last_error(const mantis_ctx* ctx);
+/* Number of kernels this context has launched since creation (bench.py's gpu_launches). */
+uint64_t mantis_launch_count(const mantis_ctx* ctx);
+/* cudaStream_t of the context, as an opaque pointer (for event timing on the launching stream). */
+void* mantis_stream(const mantis_ctx* ctx);
+
+/*
+ * Image stage of detectQuadrilaterals(): cvtColor(BGR2GRAY) -> GaussianBlur(3x3, s=3)
+ * -> Canny(T, 3T, 3) -> dilate x2 -> erode x1   (include/mantis3/QuadDetection.h:209-214;
+ * the first three are repeated verbatim by cleanImageByEdge, HypothesisEvaluation.h:323-327).
+ *
+ *   bgr          n frames of 8-bit BGR, HWC; row r of frame f starts at
+ *                bgr + f*frame_pitch_bytes + r*stride_bytes
+ *   canny_out    optional (NULL to skip): n*height*width bytes, {0,255}, the cv::Canny result
+ *   morph_out    optional: n*height*width bytes, {0,255}, after dilate x2 / erode x1
+ */
+int mantis_edges_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height,
+                       int stride_bytes, size_t frame_pitch_bytes,
+                       uint8_t* canny_out, uint8_t* morph_out, int mem);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MANTIS_CUDA_H */

@@ -1,0 +1,167 @@
+"""ctypes binding of libmantis_cuda.so (include/mantis_cuda.h).
+
+Mirrors the reference's stage functions by name where one exists
+(``detectQuadrilaterals`` image stage -> :meth:`Context.edges`, ...).  Fails loudly if the
+shared library is missing; there is no Python / CPU implementation behind it.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+MEM_HOST = 0
+MEM_DEVICE = 1
+
+
+class MantisError(RuntimeError):
+    pass
+
+
+class Config(ctypes.Structure):
+    """mantis_config: rosparams + defines of include/mantis3/Mantis3Params.h."""
+
+    _fields_ = [
+        ("canny_hysteresis", ctypes.c_int32),
+        ("polygon_epsilon", ctypes.c_int32),
+        ("search_radius_multiplier", ctypes.c_double),
+        ("grid_spacing", ctypes.c_double),
+        ("grid_size", ctypes.c_int32),
+        ("quad_stretch_factor", ctypes.c_double),
+        ("max_quad_error", ctypes.c_double),
+        ("max_angle_difference", ctypes.c_double),
+        ("projection_bias", ctypes.c_double),
+        ("color_projection_bias", ctypes.c_double),
+        ("rot_sigma", ctypes.c_double),
+        ("trans_sigma", ctypes.c_double),
+        ("particles", ctypes.c_int32),
+        ("iterations", ctypes.c_int32),
+        ("rng_seed", ctypes.c_uint64),
+    ]
+
+
+def library_path():
+    return os.path.join(_HERE, "libmantis_cuda.so")
+
+
+def build_library(force=False):
+    """Compile csrc/*.cu for sm_100a into mantis_b200/libmantis_cuda.so (in-tree)."""
+    args = ["make", "-C", os.path.join(_HERE, "csrc"), "-j8", "-s"]
+    if force:
+        args.append("-B")
+    subprocess.check_call(args)
+    return library_path()
+
+
+def load_library():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if not os.path.exists(path):
+        raise MantisError(
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(mantis_b200 has no CPU fallback)"
+        )
+    lib = ctypes.CDLL(path)
+    c = ctypes
+    lib.mantis_default_config.argtypes = [c.POINTER(Config)]
+    lib.mantis_default_config.restype = None
+    lib.mantis_create.argtypes = [c.POINTER(Config), c.c_int, c.POINTER(c.c_void_p)]
+    lib.mantis_destroy.argtypes = [c.c_void_p]
+    lib.mantis_strerror.argtypes = [c.c_int]
+    lib.mantis_strerror.restype = c.c_char_p
+    lib.mantis_last_error.argtypes = [c.c_void_p]
+    lib.mantis_last_error.restype = c.c_char_p
+    lib.mantis_launch_count.argtypes = [c.c_void_p]
+    lib.mantis_launch_count.restype = c.c_uint64
+    lib.mantis_stream.argtypes = [c.c_void_p]
+    lib.mantis_stream.restype = c.c_void_p
+    lib.mantis_edges_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
+                                       c.c_void_p, c.c_void_p, c.c_int]
+    _LIB = lib
+    return lib
+
+
+def default_config():
+    cfg = Config()
+    load_library().mantis_default_config(ctypes.byref(cfg))
+    return cfg
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return ctypes.c_void_p(a)
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+class Context:
+    """One mantis_ctx: bound to a device and a stream; not thread-safe."""
+
+    def __init__(self, device=0, config=None):
+        self._lib = load_library()
+        self.config = config if config is not None else default_config()
+        h = ctypes.c_void_p()
+        rc = self._lib.mantis_create(ctypes.byref(self.config), int(device), ctypes.byref(h))
+        if rc != 0:
+            raise MantisError(f"mantis_create: {self._lib.mantis_strerror(rc).decode()}")
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.mantis_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise MantisError(f"{what}: {self._lib.mantis_strerror(rc).decode()} "
+                              f"[{self._lib.mantis_last_error(self._h).decode()}]")
+
+    @property
+    def launch_count(self):
+        return int(self._lib.mantis_launch_count(self._h))
+
+    @property
+    def stream(self):
+        return int(self._lib.mantis_stream(self._h) or 0)
+
+    # -- image stage: detectQuadrilaterals(), QuadDetection.h:209-214 --
+    def edges(self, bgr, want_canny=True, want_morph=True):
+        """bgr: uint8 array [n, H, W, 3] (or [H, W, 3]) on the host.  Returns (canny, morph)."""
+        bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, ch = bgr.shape
+        assert ch == 3
+        canny = np.empty((n, h, w), np.uint8) if want_canny else None
+        morph = np.empty((n, h, w), np.uint8) if want_morph else None
+        rc = self._lib.mantis_edges_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, _ptr(canny), _ptr(morph),
+                                          MEM_HOST)
+        self._check(rc, "mantis_edges_batch")
+        return canny, morph
+
+    def edges_device(self, d_bgr, n, w, h, d_canny=None, d_morph=None, stride=None, pitch=None):
+        """Device-resident variant: integer device pointers (e.g. torch .data_ptr())."""
+        stride = 3 * w if stride is None else stride
+        pitch = stride * h if pitch is None else pitch
+        rc = self._lib.mantis_edges_batch(self._h, _ptr(d_bgr), n, w, h, stride, pitch, _ptr(d_canny), _ptr(d_morph),
+                                          MEM_DEVICE)
+        self._check(rc, "mantis_edges_batch")

@@ -1,0 +1,66 @@
+// ctx.h -- context object behind the C ABI (include/mantis_cuda.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/mantis_cuda.h"
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct mantis_ctx {
+    mantis_config cfg;
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    uint64_t launches = 0;
+    char err[256] = {0};
+
+    // scratch (grows monotonically)
+    DevBuf weak, strong;      // bit planes from the candidate kernel
+    DevBuf canny_bits, morph_bits;  // bit-packed results of the per-frame kernel
+    DevBuf stage_in, stage_out0, stage_out1;  // device staging for MANTIS_MEM_HOST callers
+    void* pin_in = nullptr;  size_t pin_in_cap = 0;   // pinned host staging
+    void* pin_out = nullptr; size_t pin_out_cap = 0;
+};
+
+#define MCHECK(ctx, call)                                                                  \
+    do {                                                                                   \
+        cudaError_t e__ = (call);                                                          \
+        if (e__ != cudaSuccess) {                                                          \
+            snprintf((ctx)->err, sizeof((ctx)->err), "%s:%d %s: %s", __FILE__, __LINE__, #call, \
+                     cudaGetErrorString(e__));                                             \
+            return MANTIS_ERR_CUDA;                                                        \
+        }                                                                                  \
+    } while (0)
+
+inline int ctx_reserve(mantis_ctx* c, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return MANTIS_OK;
+    if (b.p) { MCHECK(c, cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+    MCHECK(c, cudaMalloc(&b.p, bytes));
+    b.cap = bytes;
+    return MANTIS_OK;
+}
+
+inline int ctx_reserve_pinned(mantis_ctx* c, void** p, size_t* cap, size_t bytes)
+{
+    if (bytes <= *cap) return MANTIS_OK;
+    if (*p) { MCHECK(c, cudaFreeHost(*p)); *p = nullptr; *cap = 0; }
+    MCHECK(c, cudaHostAlloc(p, bytes, cudaHostAllocDefault));
+    *cap = bytes;
+    return MANTIS_OK;
+}
+
+// ---- stage launchers (defined in the .cu files) ----
+// Candidate kernel: BGR -> gray -> blur -> Sobel -> NMS -> weak / strong bit planes.
+int launch_edge_candidates(mantis_ctx* c, const uint8_t* d_bgr, int n, int w, int h, int stride,
+                           size_t frame_pitch, int low, int high, uint32_t* d_weak, uint32_t* d_strong);
+// Per-frame on-chip kernel: hysteresis closure + dilate x2 + erode x1 on bit planes.
+int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_strong, int n, int w, int h,
+                     uint32_t* d_canny_bits, uint32_t* d_morph_bits, uint8_t* d_canny_u8, uint8_t* d_morph_u8);
+
+static inline int words_per_row(int w) { return (w + 31) >> 5; }
