@@ -36,6 +36,40 @@ void mo_erode3(const uint8_t* src, int w, int h, int iters, uint8_t* dst);
 void mo_edge_stage(const uint8_t* bgr, int w, int h, int stride, int canny_low,
                    uint8_t* canny_out /* may be NULL */, uint8_t* morph_out);
 
+/* ---- contours: QuadDetection.h:216-226, HypothesisEvaluation.h:343 ---- */
+enum { MO_RETR_LIST = 1, MO_RETR_CCOMP = 2 };
+typedef struct mo_contour {
+    int first, count; /* slice of mo_contours.pts (points, not ints) */
+    int is_hole;
+    int parent;       /* discovery index of the enclosing border, -1 = frame */
+    int discovery;    /* raster discovery index of this border */
+} mo_contour;
+typedef struct mo_contours {
+    int n, npts;
+    mo_contour* c;
+    int* pts; /* x,y pairs */
+} mo_contours;
+int mo_find_contours(const uint8_t* src, int w, int h, int mode, mo_contours* out);
+void mo_free_contours(mo_contours* c);
+/* cv::approxPolyDP on an int contour; dst holds up to n points; returns the new count */
+int mo_approx_poly_dp(const int* src_xy, int n, double eps, int closed, int* dst_xy);
+
+/* ---- camera model + RNG: QuadDetection.h:294, Mantis3Types.h:125-136, PoseAdjustment.h:13-23 ---- */
+void mo_fisheye_undistort(const double* src_xy, int n, const float* K, const double* D, double* dst_xy);
+void mo_fisheye_distort(const double* src_xy, int n, const float* K, const double* D, double* dst_xy);
+void mo_ziggurat_tables(unsigned* kn, float* wn, float* fn);
+float mo_rng_randn(uint64_t* state);
+double mo_rng_gaussian(uint64_t* state, double sigma);
+
+/* ---- planar pose: CoPlanarPoseEstimator.cpp:16-58 -> RPP::Rpp (RPP.cpp:13-64) ---- */
+#define MO_RPP_MAX_POINTS 16
+int mo_rpp(const double* model3xn, const double* iprts3xn, int n, double* R9, double* t3, int* iters,
+           double* obj_err, double* img_err);
+
+/* ---- synthetic frame source (stands in for GridRenderer.cpp:211-353) ---- */
+void mo_render_grid(const double* R_w2c, const double* t_w2c, const float* K, const double* D, int w, int h,
+                    double line_width, int floor_level, uint8_t* bgr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -91,3 +91,204 @@ def edge_stage(bgr, canny_low=50):
     lib().mo_edge_stage(p, w, h, w * 3, int(canny_low), can.ctypes.data_as(ctypes.c_void_p),
                         mor.ctypes.data_as(ctypes.c_void_p))
     return can, mor
+
+
+# ---- contours ----
+class _Contour(ctypes.Structure):
+    _fields_ = [("first", ctypes.c_int), ("count", ctypes.c_int), ("is_hole", ctypes.c_int),
+                ("parent", ctypes.c_int), ("discovery", ctypes.c_int)]
+
+
+class _Contours(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_int), ("npts", ctypes.c_int), ("c", ctypes.POINTER(_Contour)),
+                ("pts", ctypes.POINTER(ctypes.c_int))]
+
+
+RETR_LIST, RETR_CCOMP = 1, 2
+
+
+def find_contours(img, mode=RETR_CCOMP):
+    """Returns (list of int32 [k,2] point arrays, list of is_hole flags) in cv2's output order."""
+    img, p = _u8(img)
+    h, w = img.shape
+    out = _Contours()
+    lib().mo_find_contours(p, w, h, int(mode), ctypes.byref(out))
+    pts = np.ctypeslib.as_array(out.pts, shape=(max(out.npts, 1), 2)).copy()
+    res, holes = [], []
+    for i in range(out.n):
+        c = out.c[i]
+        res.append(pts[c.first:c.first + c.count].astype(np.int32))
+        holes.append(bool(c.is_hole))
+    lib().mo_free_contours(ctypes.byref(out))
+    return res, holes
+
+
+def approx_poly_dp(pts, eps, closed=True):
+    pts = np.ascontiguousarray(pts, dtype=np.int32).reshape(-1, 2)
+    dst = np.empty_like(pts)
+    f = lib().mo_approx_poly_dp
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_void_p]
+    n = f(pts.ctypes.data, len(pts), float(eps), int(closed), dst.ctypes.data)
+    return dst[:n].copy()
+
+
+# ---- camera / rng ----
+def _dp(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def fisheye_undistort(pts, K, D):
+    pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 2)
+    K = np.ascontiguousarray(K, np.float32)
+    D = np.ascontiguousarray(D, np.float64)
+    out = np.empty_like(pts)
+    lib().mo_fisheye_undistort(_dp(pts), len(pts), _dp(K), _dp(D), _dp(out))
+    return out
+
+
+def fisheye_distort(pts, K, D):
+    pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 2)
+    K = np.ascontiguousarray(K, np.float32)
+    D = np.ascontiguousarray(D, np.float64)
+    out = np.empty_like(pts)
+    lib().mo_fisheye_distort(_dp(pts), len(pts), _dp(K), _dp(D), _dp(out))
+    return out
+
+
+def rng_randn(seed, n):
+    f = lib().mo_rng_randn
+    f.restype = ctypes.c_float
+    st = ctypes.c_uint64(seed if seed else 0xFFFFFFFF)
+    return np.array([f(ctypes.byref(st)) for _ in range(n)], np.float32)
+
+
+def ziggurat_tables():
+    kn = np.empty(128, np.uint32)
+    wn = np.empty(128, np.float32)
+    fn = np.empty(128, np.float32)
+    lib().mo_ziggurat_tables(_dp(kn), _dp(wn), _dp(fn))
+    return kn, wn, fn
+
+
+def rpp(model3xn, iprts3xn):
+    """Returns (ok, R[3,3], t[3], iters, obj_err, img_err)."""
+    m = np.ascontiguousarray(model3xn, np.float64)
+    ip = np.ascontiguousarray(iprts3xn, np.float64)
+    R = np.zeros(9)
+    t = np.zeros(3)
+    it = ctypes.c_int()
+    oe = ctypes.c_double()
+    ie = ctypes.c_double()
+    ok = lib().mo_rpp(_dp(m), _dp(ip), m.shape[1], _dp(R), _dp(t), ctypes.byref(it), ctypes.byref(oe), ctypes.byref(ie))
+    return bool(ok), R.reshape(3, 3), t, it.value, oe.value, ie.value
+
+
+# ---- map (params/map.yaml geometry; params/matGen_dense.m) ----
+def make_map(spacing=0.32):
+    """white [646,3], red [37,3], green [37,3]: the values params/map.yaml holds (printed with
+    %f by matGen_dense.m, parsed back with atof by parseCoordinatesFromString)."""
+    r6 = lambda v: float("%f" % v)
+    white = []
+    for y in np.arange(-3.5, 3.5 + 1e-9, 1.0):
+        for x in np.arange(-4.5, 4.5 + 1e-9, 0.25):
+            white.append((r6(spacing * x), r6(spacing * y), 0.0))
+    for x in np.arange(-4.5, 4.5 + 1e-9, 1.0):
+        for y in np.arange(-4.25, 4.25 + 1e-9, 0.25):
+            white.append((r6(spacing * x), r6(spacing * y), 0.0))
+    green = [(r6(spacing * x), r6(4.5 * spacing), 0.0) for x in np.arange(-4.5, 4.5 + 1e-9, 0.25)]
+    red = [(r6(spacing * x), r6(-4.5 * spacing), 0.0) for x in np.arange(-4.5, 4.5 + 1e-9, 0.25)]
+    return np.array(white), np.array(red), np.array(green)
+
+
+# ---- pipeline ----
+MAX_QUADS = 1024
+
+
+class _Tf(ctypes.Structure):
+    _fields_ = [("R", ctypes.c_double * 9), ("t", ctypes.c_double * 3)]
+
+
+class _Hyp(ctypes.Structure):
+    _fields_ = [("c2w", _Tf), ("w2c", _Tf), ("q", ctypes.c_double * 4), ("error", ctypes.c_double)]
+
+
+class Params(ctypes.Structure):
+    _fields_ = [("canny_hysteresis", ctypes.c_int), ("polygon_epsilon", ctypes.c_int),
+                ("search_radius_multiplier", ctypes.c_double), ("grid_spacing", ctypes.c_double),
+                ("grid_size", ctypes.c_int), ("quad_stretch_factor", ctypes.c_double),
+                ("max_quad_error", ctypes.c_double), ("max_angle_difference", ctypes.c_double),
+                ("projection_bias", ctypes.c_double), ("color_projection_bias", ctypes.c_double),
+                ("rot_sigma", ctypes.c_double), ("trans_sigma", ctypes.c_double),
+                ("particles", ctypes.c_int), ("iterations", ctypes.c_int), ("rng_seed", ctypes.c_uint64)]
+
+
+class _Map(ctypes.Structure):
+    _fields_ = [("n_white", ctypes.c_int), ("n_red", ctypes.c_int), ("n_green", ctypes.c_int),
+                ("white", ctypes.c_void_p), ("red", ctypes.c_void_p), ("green", ctypes.c_void_p)]
+
+
+class Trace(ctypes.Structure):
+    _fields_ = [("status", ctypes.c_int), ("n_contours", ctypes.c_int), ("n_quads_raw", ctypes.c_int),
+                ("n_quads", ctypes.c_int),
+                ("quad_corners", (ctypes.c_int * 8) * MAX_QUADS),
+                ("quad_test_px", (ctypes.c_double * 8) * MAX_QUADS),
+                ("quad_test_norm", (ctypes.c_double * 8) * MAX_QUADS),
+                ("n_hyps_generated", ctypes.c_int), ("n_hyps_cluster", ctypes.c_int),
+                ("quad_pass", ctypes.c_int * MAX_QUADS), ("quad_img_err", ctypes.c_double * MAX_QUADS),
+                ("first_best", _Hyp), ("optimized", _Hyp), ("shift_err", ctypes.c_double * 81),
+                ("yaw_err", ctypes.c_double * 4), ("best_rot", ctypes.c_int), ("min_yaw_diff", ctypes.c_double),
+                ("final_hyp", _Hyp), ("pos", ctypes.c_double * 3), ("quat_xyzw", ctypes.c_double * 4),
+                ("error", ctypes.c_double), ("n_scored", ctypes.c_long)]
+
+
+def default_params():
+    p = Params()
+    lib().mo_default_params(ctypes.byref(p))
+    return p
+
+
+_MAP_KEEP = {}
+
+
+def _map_struct(maps=None):
+    key = id(maps)
+    if key not in _MAP_KEEP:
+        w, r, g = maps if maps is not None else make_map()
+        w, r, g = (np.ascontiguousarray(a, np.float64) for a in (w, r, g))
+        m = _Map(len(w), len(r), len(g), w.ctypes.data, r.ctypes.data, g.ctypes.data)
+        _MAP_KEEP[key] = (m, w, r, g)
+    return _MAP_KEEP[key][0]
+
+
+def localize(bgr, K, D, params=None, maps=None, want_mask=False):
+    """Whole-frame oracle: returns (Trace, mask or None)."""
+    bgr, p = _u8(bgr)
+    h, w, _ = bgr.shape
+    K = np.ascontiguousarray(K, np.float32)
+    D = np.ascontiguousarray(D, np.float64)
+    prm = params if params is not None else default_params()
+    tr = Trace()
+    mask = np.empty((h, w), np.uint8) if want_mask else None
+    lib().mo_localize(p, w, h, 3 * w, _dp(K), _dp(D), ctypes.byref(prm), ctypes.byref(_map_struct(maps)),
+                      ctypes.byref(tr), _dp(mask) if want_mask else None)
+    return tr, mask
+
+
+def clean_mask(canny):
+    canny, p = _u8(canny)
+    h, w = canny.shape
+    out = np.empty((h, w), np.uint8)
+    lib().mo_clean_mask(p, w, h, _dp(out))
+    return out
+
+
+def render_grid(R_w2c, t_w2c, K, D, w, h, line_width=0.04, floor_level=30):
+    R = np.ascontiguousarray(R_w2c, np.float64)
+    t = np.ascontiguousarray(t_w2c, np.float64)
+    K = np.ascontiguousarray(K, np.float32)
+    D = np.ascontiguousarray(D, np.float64)
+    out = np.empty((h, w, 3), np.uint8)
+    f = lib().mo_render_grid
+    f.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_void_p]
+    f(_dp(R), _dp(t), _dp(K), _dp(D), w, h, float(line_width), int(floor_level), _dp(out))
+    return out
