@@ -93,6 +93,38 @@ int mantis_edges_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, in
                        int stride_bytes, size_t frame_pitch_bytes,
                        uint8_t* canny_out, uint8_t* morph_out, int mem);
 
+/*
+ * Edge mask of cleanImageByEdge() (include/mantis3/HypothesisEvaluation.h:319-386): the image the
+ * WHITE scoring reads is `bgr where mask else 0`; the library keeps the mask as one bit per pixel
+ * and never materialises the masked copy.  mask_out: n*height*width bytes {0,255}.
+ */
+int mantis_mask_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height,
+                      int stride_bytes, size_t frame_pitch_bytes, uint8_t* mask_out, int mem);
+
+/*
+ * Grid-cell (quad) extraction, the rest of detectQuadrilaterals():
+ * findContours(RETR_CCOMP, CHAIN_APPROX_SIMPLE) -> approxPolyDP(eps, closed) -> keep 4-gons ->
+ * Quadrilateral ctor -> removeDuplicateQuads   (include/mantis3/QuadDetection.h:13-66,115-171,216-228).
+ * Quads come out in the reference's order (OpenCV's RETR_CCOMP contour order).
+ */
+#define MANTIS_MAX_QUADS 256
+enum { /* mantis_frame_quads.flags: capacity limits of the on-chip stage hit for this frame */
+    MANTIS_FLAG_BORDER_OVERFLOW = 1, /* more than 1024 contours */
+    MANTIS_FLAG_POINT_OVERFLOW = 2,  /* more than 65536 contour vertices */
+    MANTIS_FLAG_QUAD_OVERFLOW = 4    /* more than MANTIS_MAX_QUADS 4-gons */
+};
+typedef struct mantis_frame_quads {
+    int32_t n_contours;   /* contours found (f->contours.size()) */
+    int32_t n_quads_raw;  /* 4-gons before removeDuplicateQuads */
+    int32_t n_quads;      /* f->quads.size() */
+    int32_t flags;
+    int32_t corners[MANTIS_MAX_QUADS][8]; /* Quadrilateral::contour, x,y of 4 vertices */
+    double test_px[MANTIS_MAX_QUADS][8];  /* Quadrilateral::test_points (pixels, before undistortion) */
+} mantis_frame_quads;
+
+int mantis_quads_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height,
+                       int stride_bytes, size_t frame_pitch_bytes, mantis_frame_quads* out, int mem);
+
 #ifdef __cplusplus
 }
 #endif

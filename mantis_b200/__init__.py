@@ -11,6 +11,7 @@ from .binding import (  # noqa: F401
     MEM_HOST,
     Config,
     Context,
+    FrameQuads,
     MantisError,
     build_library,
     library_path,

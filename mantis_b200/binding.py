@@ -43,6 +43,17 @@ class Config(ctypes.Structure):
     ]
 
 
+MAX_QUADS = 256
+
+
+class FrameQuads(ctypes.Structure):
+    """mantis_frame_quads."""
+
+    _fields_ = [("n_contours", ctypes.c_int32), ("n_quads_raw", ctypes.c_int32), ("n_quads", ctypes.c_int32),
+                ("flags", ctypes.c_int32), ("corners", (ctypes.c_int32 * 8) * MAX_QUADS),
+                ("test_px", (ctypes.c_double * 8) * MAX_QUADS)]
+
+
 def library_path():
     return os.path.join(_HERE, "libmantis_cuda.so")
 
@@ -82,6 +93,10 @@ def load_library():
     lib.mantis_stream.restype = c.c_void_p
     lib.mantis_edges_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
                                        c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_mask_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
+                                      c.c_void_p, c.c_int]
+    lib.mantis_quads_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
+                                       c.c_void_p, c.c_int]
     _LIB = lib
     return lib
 
@@ -165,3 +180,26 @@ class Context:
         rc = self._lib.mantis_edges_batch(self._h, _ptr(d_bgr), n, w, h, stride, pitch, _ptr(d_canny), _ptr(d_morph),
                                           MEM_DEVICE)
         self._check(rc, "mantis_edges_batch")
+
+    # -- cleanImageByEdge mask, HypothesisEvaluation.h:319-386 --
+    def edge_mask(self, bgr):
+        bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, _ = bgr.shape
+        mask = np.empty((n, h, w), np.uint8)
+        rc = self._lib.mantis_mask_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, _ptr(mask), MEM_HOST)
+        self._check(rc, "mantis_mask_batch")
+        return mask
+
+    # -- detectQuadrilaterals(), QuadDetection.h:203-287 --
+    def quads(self, bgr):
+        """Returns one FrameQuads record per frame."""
+        bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, _ = bgr.shape
+        out = (FrameQuads * n)()
+        rc = self._lib.mantis_quads_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, ctypes.addressof(out), MEM_HOST)
+        self._check(rc, "mantis_quads_batch")
+        return out

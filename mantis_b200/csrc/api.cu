@@ -66,7 +66,7 @@ int mantis_destroy(mantis_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_out0,
-                      &c->stage_out1};
+                      &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->frame_quads};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->pin_in) cudaFreeHost(c->pin_in);
@@ -80,55 +80,139 @@ const char* mantis_last_error(const mantis_ctx* c) { return c ? c->err : ""; }
 uint64_t mantis_launch_count(const mantis_ctx* c) { return c ? c->launches : 0; }
 void* mantis_stream(const mantis_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
-int mantis_edges_batch(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
-                       size_t frame_pitch_bytes, uint8_t* canny_out, uint8_t* morph_out, int mem)
+// ---- shared plumbing --------------------------------------------------------------------
+static int check_frames(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                        size_t frame_pitch_bytes, int mem)
 {
     if (!c) return MANTIS_ERR_INVALID;
-    if (n == 0) return MANTIS_OK;
-    if (!bgr || n < 0 || width <= 0 || height <= 0 || stride_bytes < 3 * width ||
+    if (!bgr || n < 0 || width <= 0 || height <= 0 || width > 32767 || height > 32767 || stride_bytes < 3 * width ||
         frame_pitch_bytes < (size_t)stride_bytes * (height - 1) + (size_t)3 * width ||
         (mem != MANTIS_MEM_HOST && mem != MANTIS_MEM_DEVICE))
         return MANTIS_ERR_INVALID;
-    MCHECK(c, cudaSetDevice(c->device));
+    return MANTIS_OK;
+}
 
-    const int WW = words_per_row(width);
-    const size_t plane_bytes = (size_t)n * height * WW * sizeof(uint32_t);
-    const size_t map_bytes = (size_t)n * height * width;
-    int rc;
-    if ((rc = ctx_reserve(c, c->weak, plane_bytes)) || (rc = ctx_reserve(c, c->strong, plane_bytes))) return rc;
-
-    const uint8_t* d_in = bgr;
-    uint8_t* d_canny = canny_out;
-    uint8_t* d_morph = morph_out;
+// Brings the frames onto the device if the caller holds them on the host.
+static int stage_input(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                       size_t frame_pitch_bytes, int mem, const uint8_t** d_in)
+{
+    *d_in = bgr;
     if (mem == MANTIS_MEM_HOST) {
-        // stage the whole batch: H2D on the context stream, results D2H after the kernels
         size_t in_bytes = frame_pitch_bytes * (size_t)(n - 1) + (size_t)stride_bytes * (height - 1) + 3 * (size_t)width;
+        int rc;
         if ((rc = ctx_reserve(c, c->stage_in, in_bytes))) return rc;
         MCHECK(c, cudaMemcpyAsync(c->stage_in.p, bgr, in_bytes, cudaMemcpyHostToDevice, c->stream));
-        d_in = (const uint8_t*)c->stage_in.p;
-        if (canny_out) { if ((rc = ctx_reserve(c, c->stage_out0, map_bytes))) return rc; d_canny = (uint8_t*)c->stage_out0.p; }
-        if (morph_out) { if ((rc = ctx_reserve(c, c->stage_out1, map_bytes))) return rc; d_morph = (uint8_t*)c->stage_out1.p; }
+        *d_in = (const uint8_t*)c->stage_in.p;
     }
+    return MANTIS_OK;
+}
 
+// K1 + K2 over a batch already on the device.  `out` pointers are per-batch bases.
+int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int height, int stride_bytes,
+                   size_t frame_pitch_bytes, const EdgeOutputs& out)
+{
+    const int WW = words_per_row(width);
+    const size_t plane_bytes = (size_t)n * height * WW * sizeof(uint32_t);
+    int rc;
+    if ((rc = ctx_reserve(c, c->weak, plane_bytes)) || (rc = ctx_reserve(c, c->strong, plane_bytes))) return rc;
     const int low = c->cfg.canny_hysteresis, high = 3 * c->cfg.canny_hysteresis;
     // gridDim.z is limited to 65535 frames per launch
     for (int f0 = 0; f0 < n; f0 += 32768) {
         int nf = (n - f0 < 32768) ? (n - f0) : 32768;
-        size_t poff = (size_t)f0 * height * WW;
+        size_t poff = (size_t)f0 * height * WW, moff = (size_t)f0 * height * width;
         if ((rc = launch_edge_candidates(c, d_in + (size_t)f0 * frame_pitch_bytes, nf, width, height, stride_bytes,
                                          frame_pitch_bytes, low, high, (uint32_t*)c->weak.p + poff,
                                          (uint32_t*)c->strong.p + poff)))
             return rc;
-        size_t moff = (size_t)f0 * height * width;
-        if ((rc = launch_edge_link(c, (uint32_t*)c->weak.p + poff, (uint32_t*)c->strong.p + poff, nf, width, height,
-                                   nullptr, nullptr, d_canny ? d_canny + moff : nullptr,
-                                   d_morph ? d_morph + moff : nullptr)))
+        EdgeOutputs eo;
+        eo.canny_bits = out.canny_bits ? out.canny_bits + poff : nullptr;
+        eo.morph_bits = out.morph_bits ? out.morph_bits + poff : nullptr;
+        eo.mask_bits = out.mask_bits ? out.mask_bits + poff : nullptr;
+        eo.canny_u8 = out.canny_u8 ? out.canny_u8 + moff : nullptr;
+        eo.morph_u8 = out.morph_u8 ? out.morph_u8 + moff : nullptr;
+        eo.mask_u8 = out.mask_u8 ? out.mask_u8 + moff : nullptr;
+        if ((rc = launch_edge_link(c, (uint32_t*)c->weak.p + poff, (uint32_t*)c->strong.p + poff, nf, width, height, eo)))
             return rc;
     }
+    return MANTIS_OK;
+}
+
+int mantis_edges_batch(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                       size_t frame_pitch_bytes, uint8_t* canny_out, uint8_t* morph_out, int mem)
+{
+    int rc = check_frames(c, bgr, n, width, height, stride_bytes, frame_pitch_bytes, mem);
+    if (rc) return rc;
+    if (n == 0) return MANTIS_OK;
+    MCHECK(c, cudaSetDevice(c->device));
+    const size_t map_bytes = (size_t)n * height * width;
+    const uint8_t* d_in;
+    if ((rc = stage_input(c, bgr, n, width, height, stride_bytes, frame_pitch_bytes, mem, &d_in))) return rc;
+    EdgeOutputs eo;
+    eo.canny_u8 = canny_out;
+    eo.morph_u8 = morph_out;
     if (mem == MANTIS_MEM_HOST) {
-        if (canny_out) MCHECK(c, cudaMemcpyAsync(canny_out, d_canny, map_bytes, cudaMemcpyDeviceToHost, c->stream));
-        if (morph_out) MCHECK(c, cudaMemcpyAsync(morph_out, d_morph, map_bytes, cudaMemcpyDeviceToHost, c->stream));
+        if (canny_out) { if ((rc = ctx_reserve(c, c->stage_out0, map_bytes))) return rc; eo.canny_u8 = (uint8_t*)c->stage_out0.p; }
+        if (morph_out) { if ((rc = ctx_reserve(c, c->stage_out1, map_bytes))) return rc; eo.morph_u8 = (uint8_t*)c->stage_out1.p; }
     }
+    if ((rc = run_edge_stage(c, d_in, n, width, height, stride_bytes, frame_pitch_bytes, eo))) return rc;
+    if (mem == MANTIS_MEM_HOST) {
+        if (canny_out) MCHECK(c, cudaMemcpyAsync(canny_out, eo.canny_u8, map_bytes, cudaMemcpyDeviceToHost, c->stream));
+        if (morph_out) MCHECK(c, cudaMemcpyAsync(morph_out, eo.morph_u8, map_bytes, cudaMemcpyDeviceToHost, c->stream));
+    }
+    MCHECK(c, cudaStreamSynchronize(c->stream));
+    return MANTIS_OK;
+}
+
+int mantis_mask_batch(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                      size_t frame_pitch_bytes, uint8_t* mask_out, int mem)
+{
+    int rc = check_frames(c, bgr, n, width, height, stride_bytes, frame_pitch_bytes, mem);
+    if (rc) return rc;
+    if (!mask_out) return MANTIS_ERR_INVALID;
+    if (n == 0) return MANTIS_OK;
+    MCHECK(c, cudaSetDevice(c->device));
+    const uint8_t* d_in;
+    if ((rc = stage_input(c, bgr, n, width, height, stride_bytes, frame_pitch_bytes, mem, &d_in))) return rc;
+    const size_t plane_bytes = (size_t)n * height * words_per_row(width) * sizeof(uint32_t);
+    const size_t map_bytes = (size_t)n * height * width;
+    if ((rc = ctx_reserve(c, c->canny_bits, plane_bytes))) return rc;
+    EdgeOutputs eo;
+    eo.canny_bits = (uint32_t*)c->canny_bits.p;
+    eo.mask_u8 = mask_out;
+    if (mem == MANTIS_MEM_HOST) {
+        if ((rc = ctx_reserve(c, c->stage_out0, map_bytes))) return rc;
+        eo.mask_u8 = (uint8_t*)c->stage_out0.p;
+    }
+    if ((rc = run_edge_stage(c, d_in, n, width, height, stride_bytes, frame_pitch_bytes, eo))) return rc;
+    if (mem == MANTIS_MEM_HOST)
+        MCHECK(c, cudaMemcpyAsync(mask_out, eo.mask_u8, map_bytes, cudaMemcpyDeviceToHost, c->stream));
+    MCHECK(c, cudaStreamSynchronize(c->stream));
+    return MANTIS_OK;
+}
+
+int mantis_quads_batch(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                       size_t frame_pitch_bytes, mantis_frame_quads* out, int mem)
+{
+    int rc = check_frames(c, bgr, n, width, height, stride_bytes, frame_pitch_bytes, mem);
+    if (rc) return rc;
+    if (!out) return MANTIS_ERR_INVALID;
+    if (n == 0) return MANTIS_OK;
+    MCHECK(c, cudaSetDevice(c->device));
+    const uint8_t* d_in;
+    if ((rc = stage_input(c, bgr, n, width, height, stride_bytes, frame_pitch_bytes, mem, &d_in))) return rc;
+    const size_t plane_bytes = (size_t)n * height * words_per_row(width) * sizeof(uint32_t);
+    if ((rc = ctx_reserve(c, c->morph_bits, plane_bytes))) return rc;
+    EdgeOutputs eo;
+    eo.morph_bits = (uint32_t*)c->morph_bits.p;
+    if ((rc = run_edge_stage(c, d_in, n, width, height, stride_bytes, frame_pitch_bytes, eo))) return rc;
+    mantis_frame_quads* d_out = out;
+    if (mem == MANTIS_MEM_HOST) {
+        if ((rc = ctx_reserve(c, c->frame_quads, (size_t)n * sizeof(mantis_frame_quads)))) return rc;
+        d_out = (mantis_frame_quads*)c->frame_quads.p;
+    }
+    if ((rc = launch_quads(c, eo.morph_bits, n, width, height, d_out))) return rc;
+    if (mem == MANTIS_MEM_HOST)
+        MCHECK(c, cudaMemcpyAsync(out, d_out, (size_t)n * sizeof(mantis_frame_quads), cudaMemcpyDeviceToHost, c->stream));
     MCHECK(c, cudaStreamSynchronize(c->stream));
     return MANTIS_OK;
 }

@@ -22,6 +22,8 @@ struct mantis_ctx {
     // scratch (grows monotonically)
     DevBuf weak, strong;      // bit planes from the candidate kernel
     DevBuf canny_bits, morph_bits;  // bit-packed results of the per-frame kernel
+    DevBuf q_pts, q_dst, q_stack, q_owner;   // quad kernel scratch (per resident CTA)
+    DevBuf frame_quads;                      // FrameQuads[n]
     DevBuf stage_in, stage_out0, stage_out1;  // device staging for MANTIS_MEM_HOST callers
     void* pin_in = nullptr;  size_t pin_in_cap = 0;   // pinned host staging
     void* pin_out = nullptr; size_t pin_out_cap = 0;
@@ -59,8 +61,19 @@ inline int ctx_reserve_pinned(mantis_ctx* c, void** p, size_t* cap, size_t bytes
 // Candidate kernel: BGR -> gray -> blur -> Sobel -> NMS -> weak / strong bit planes.
 int launch_edge_candidates(mantis_ctx* c, const uint8_t* d_bgr, int n, int w, int h, int stride,
                            size_t frame_pitch, int low, int high, uint32_t* d_weak, uint32_t* d_strong);
-// Per-frame on-chip kernel: hysteresis closure + dilate x2 + erode x1 on bit planes.
+// Per-frame on-chip kernel: hysteresis closure, dilate x2 + erode x1, edge mask; every output optional.
+struct EdgeOutputs {
+    uint32_t* canny_bits = nullptr;
+    uint32_t* morph_bits = nullptr;
+    uint32_t* mask_bits = nullptr;
+    uint8_t* canny_u8 = nullptr;
+    uint8_t* morph_u8 = nullptr;
+    uint8_t* mask_u8 = nullptr;
+};
 int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_strong, int n, int w, int h,
-                     uint32_t* d_canny_bits, uint32_t* d_morph_bits, uint8_t* d_canny_u8, uint8_t* d_morph_u8);
+                     const EdgeOutputs& out);
+
+// Contours -> approxPolyDP -> 4-gons -> de-duplicated quads, per frame, in OpenCV's order.
+int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int h, mantis_frame_quads* d_out);
 
 static inline int words_per_row(int w) { return (w + 31) >> 5; }

@@ -1,14 +1,18 @@
-// edge_link.cu -- K2: per-frame on-chip Canny hysteresis closure + dilate x2 + erode x1.
+// edge_link.cu -- K2: per-frame on-chip Canny hysteresis closure, dilate x2 / erode x1, and the
+// cleanImageByEdge mask chain, all on bit-packed planes that never leave shared memory.
 //
-// Completes cv::Canny (the 8-connected hysteresis closure, QuadDetection.h:212) and applies
-// cv::dilate(iter 2) / cv::erode(iter 1) (:213-214) on bit-packed planes that never leave
-// shared memory: one thread-block cluster per frame, the rows of the frame split across
-// the CTAs of the cluster, halo rows exchanged through distributed shared memory.
+//   cv::Canny's 8-connected hysteresis closure                 QuadDetection.h:212
+//   cv::dilate(iter 2) / cv::erode(iter 1)                     QuadDetection.h:213-214
+//   cleanImageByEdge: MORPH_GRADIENT (3x3 cross), NOT, findContours(RETR_LIST)+drawContours
+//   (== boundary pixels of the NOT image), OR with Canny, closes of 3/4/5 iterations,
+//   erode 3                                                    HypothesisEvaluation.h:336-372
 //
+// One thread-block cluster per frame: the rows of the frame are split across the CTAs of the
+// cluster and halo rows are exchanged through distributed shared memory (DSMEM).
 //   closure : E <- strong;  repeat E <- weak & flood(E | dilate3x3(E)) until stable.  In-word
 //             horizontal runs are filled in O(1) with the carry trick ((M+S)^M)&M.
-//   dilate  : 3x3 max, out-of-image pixels never win  == OR with zero halo
-//   erode   : 3x3 min, out-of-image pixels never win  == AND with all-ones halo
+//   3x3 max : out-of-image pixels never win == OR with 0 outside
+//   3x3 min : out-of-image pixels never win == AND with 1 outside
 #include <cooperative_groups.h>
 #include "ctx.h"
 
@@ -35,91 +39,136 @@ __device__ __forceinline__ uint32_t expand4(uint32_t nib)
 struct LinkArgs {
     const uint32_t* weak;
     const uint32_t* strong;
-    uint32_t* canny_bits;
+    uint32_t* canny_bits;  // required when mask output is requested
     uint32_t* morph_bits;
+    uint32_t* mask_bits;
     uint8_t* canny_u8;
     uint8_t* morph_u8;
+    uint8_t* mask_u8;
     int W, H, WW, HC;  // HC = rows per CTA
 };
 
-// write rows [row0, row0+nrows) of a bit plane held in smem (local rows 1..nrows) as u8 {0,255}
-__device__ void store_u8(const uint32_t* s, int WW, int W, int row0, int nrows, uint8_t* dst)
+// Geometry of this CTA's band of rows.  Planes are stored as (HC+2) x WW words: local row 0
+// and nrows+1 are halo rows (copies of the neighbouring CTAs' boundary rows).
+struct Band {
+    int W, H, WW, HC, rank, last_rank, row0, nrows;
+    uint32_t last_mask;
+};
+
+// write rows of a bit plane held in smem (local rows 1..nrows) as u8 {0,255}
+__device__ void store_u8(const uint32_t* s, const Band& b, uint8_t* dst)
 {
+    const int W = b.W, WW = b.WW;
     if ((W & 15) == 0 && (((uintptr_t)dst) & 15) == 0) {
         int halves = W >> 4;  // 16-px groups per row
-        for (int i = threadIdx.x; i < nrows * halves; i += LNT) {
+        for (int i = threadIdx.x; i < b.nrows * halves; i += LNT) {
             int r = i / halves, hx = i - r * halves;
             uint32_t w = s[(r + 1) * WW + (hx >> 1)];
-            uint32_t b = (hx & 1) ? (w >> 16) : (w & 0xffffu);
+            uint32_t v16 = (hx & 1) ? (w >> 16) : (w & 0xffffu);
             uint4 v;
-            v.x = expand4(b & 15u);
-            v.y = expand4((b >> 4) & 15u);
-            v.z = expand4((b >> 8) & 15u);
-            v.w = expand4((b >> 12) & 15u);
-            *reinterpret_cast<uint4*>(dst + (size_t)(row0 + r) * W + hx * 16) = v;
+            v.x = expand4(v16 & 15u);
+            v.y = expand4((v16 >> 4) & 15u);
+            v.z = expand4((v16 >> 8) & 15u);
+            v.w = expand4((v16 >> 12) & 15u);
+            *reinterpret_cast<uint4*>(dst + (size_t)(b.row0 + r) * W + hx * 16) = v;
         }
     } else {
-        for (int i = threadIdx.x; i < nrows * W; i += LNT) {
+        for (int i = threadIdx.x; i < b.nrows * W; i += LNT) {
             int r = i / W, x = i - r * W;
             uint32_t w = s[(r + 1) * WW + (x >> 5)];
-            dst[(size_t)(row0 + r) * W + x] = ((w >> (x & 31)) & 1u) ? 255 : 0;
+            dst[(size_t)(b.row0 + r) * W + x] = ((w >> (x & 31)) & 1u) ? 255 : 0;
         }
     }
 }
 
-// Pull the neighbours' boundary rows of plane `s` (same smem offset in every CTA) into my halo
-// rows 0 and nrows+1.  `fill` is the value used where there is no neighbour (image border).
-// Returns (per thread) whether a halo word changed.
-__device__ int pull_halo(cg::cluster_group& cluster, uint32_t* s, int WW, int HC, int nrows, int rank,
-                         int last_rank, const int* s_nrows_dummy, uint32_t fill)
+__device__ void store_bits(const uint32_t* s, const Band& b, uint32_t* dst_plane)
 {
-    (void)s_nrows_dummy;
+    for (int i = threadIdx.x; i < b.nrows * b.WW; i += LNT) dst_plane[(size_t)b.row0 * b.WW + i] = s[b.WW + i];
+}
+
+// Pull the neighbours' boundary rows of plane `s` (same smem offset in every CTA) into my halo
+// rows.  Returns (per thread) whether a halo word changed.  Rows outside the image are never
+// read through the halo (see row_word), so nothing is written for them.
+__device__ int pull_halo(cg::cluster_group& cluster, uint32_t* s, const Band& b)
+{
     int changed = 0;
+    const int WW = b.WW;
     for (int j = threadIdx.x; j < 2 * WW; j += LNT) {
         int top = j < WW;
         int jj = top ? j : j - WW;
-        uint32_t v = fill;
+        uint32_t v;
+        uint32_t* dst;
         if (top) {
-            if (rank > 0) {
-                const uint32_t* nb = cluster.map_shared_rank(s, rank - 1);
-                v = nb[HC * WW + jj];  // every non-last CTA owns exactly HC rows
-            }
+            if (b.rank == 0) continue;
+            const uint32_t* nb = cluster.map_shared_rank(s, b.rank - 1);
+            v = nb[b.HC * WW + jj];  // every non-last CTA owns exactly HC rows
+            dst = &s[jj];
         } else {
-            if (rank < last_rank) {
-                const uint32_t* nb = cluster.map_shared_rank(s, rank + 1);
-                v = nb[1 * WW + jj];
-            }
+            if (b.rank >= b.last_rank) continue;
+            const uint32_t* nb = cluster.map_shared_rank(s, b.rank + 1);
+            v = nb[1 * WW + jj];
+            dst = &s[(b.nrows + 1) * WW + jj];
         }
-        uint32_t* dst = top ? &s[jj] : &s[(nrows + 1) * WW + jj];
         if (*dst != v) { *dst = v; changed = 1; }
     }
     return changed;
 }
 
-template <bool DILATE>
-__device__ void morph3(const uint32_t* src, uint32_t* dst, int WW, int nrows, uint32_t last_mask)
+// Make the halo rows of `s` current: cluster barrier (everyone finished writing), pull, block
+// barrier.  For a single-CTA frame only the block barrier is needed.
+__device__ void refresh_halo(cg::cluster_group& cluster, uint32_t* s, const Band& b, int CS)
 {
-    for (int i = threadIdx.x; i < nrows * WW; i += LNT) {
-        int r = i / WW + 1, j = i - (r - 1) * WW;
-        const uint32_t* p = src + r * WW + j;
-        uint32_t vc, vl, vr;
-        if (DILATE) {
-            vc = p[-WW] | p[0] | p[WW];
-            vl = (j > 0) ? (p[-WW - 1] | p[-1] | p[WW - 1]) >> 31 : 0u;
-            vr = (j < WW - 1) ? (p[-WW + 1] | p[1] | p[WW + 1]) << 31 : 0u;
-            uint32_t o = vc | (vc << 1) | (vc >> 1) | vl | vr;
-            if (j == WW - 1) o &= last_mask;
-            dst[r * WW + j] = o;
-        } else {
-            uint32_t inv = (j == WW - 1) ? ~last_mask : 0u;  // out-of-image columns never win the min
-            vc = (p[-WW] | inv) & (p[0] | inv) & (p[WW] | inv);
-            vl = (j > 0) ? (p[-WW - 1] & p[-1] & p[WW - 1]) >> 31 : 1u;
-            uint32_t invr = (j + 1 == WW - 1) ? ~last_mask : 0u;
-            vr = (j < WW - 1) ? ((p[-WW + 1] | invr) & (p[1] | invr) & (p[WW + 1] | invr)) << 31 : 0x80000000u;
-            uint32_t o = vc & ((vc << 1) | vl) & ((vc >> 1) | vr);
-            if (j == WW - 1) o &= last_mask;
-            dst[r * WW + j] = o;
-        }
+    if (CS > 1) {
+        cluster.sync();
+        pull_halo(cluster, s, b);
+    }
+    __syncthreads();
+}
+
+// word (local row lr in 0..nrows+1, column j) of a plane, with `fill` for anything outside the
+// image (rows above 0 / below H-1, columns left of 0 / right of W-1 including the unused
+// bits of the last word).
+__device__ __forceinline__ uint32_t row_word(const uint32_t* s, const Band& b, int lr, int j, uint32_t fill)
+{
+    int gr = b.row0 + lr - 1;
+    if (gr < 0 || gr >= b.H || j < 0 || j >= b.WW) return fill;
+    uint32_t w = s[lr * b.WW + j];
+    if (j == b.WW - 1) w |= (fill & ~b.last_mask);
+    return w;
+}
+
+// 3-row vertical combine + horizontal neighbours for one output word.
+// FULL: 3x3 box; otherwise the 3x3 cross.  OR: max with 0 outside; otherwise min with 1 outside.
+template <bool OR, bool FULL>
+__device__ __forceinline__ uint32_t stencil(const uint32_t* s, const Band& b, int lr, int j)
+{
+    const uint32_t fill = OR ? 0u : 0xffffffffu;
+    uint32_t u = row_word(s, b, lr - 1, j, fill), c = row_word(s, b, lr, j, fill), d = row_word(s, b, lr + 1, j, fill);
+    uint32_t cl = row_word(s, b, lr, j - 1, fill), cr = row_word(s, b, lr, j + 1, fill);
+    uint32_t v, vl, vr;  // columns whose left / right neighbours are taken
+    if (FULL) {
+        uint32_t ul = row_word(s, b, lr - 1, j - 1, fill), ur = row_word(s, b, lr - 1, j + 1, fill);
+        uint32_t dl = row_word(s, b, lr + 1, j - 1, fill), dr = row_word(s, b, lr + 1, j + 1, fill);
+        v = OR ? (u | c | d) : (u & c & d);
+        vl = OR ? (ul | cl | dl) : (ul & cl & dl);
+        vr = OR ? (ur | cr | dr) : (ur & cr & dr);
+    } else {
+        v = c; vl = cl; vr = cr;
+    }
+    uint32_t left = (v << 1) | (vl >> 31), right = (v >> 1) | (vr << 31);
+    uint32_t o;
+    if (FULL) o = OR ? (v | left | right) : (v & left & right);
+    else o = OR ? (u | c | d | left | right) : (u & c & d & left & right);
+    if (j == b.WW - 1) o &= b.last_mask;
+    return o;
+}
+
+template <bool OR>
+__device__ void box3(const uint32_t* src, uint32_t* dst, const Band& b)
+{
+    for (int i = threadIdx.x; i < b.nrows * b.WW; i += LNT) {
+        int lr = i / b.WW + 1, j = i - (lr - 1) * b.WW;
+        dst[lr * b.WW + j] = stencil<OR, true>(src, b, lr, j);
     }
 }
 
@@ -130,25 +179,26 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
 
     cg::cluster_group cluster = cg::this_cluster();
     const int CS = cluster_size;
-    const int rank = (CS > 1) ? (int)cluster.block_rank() : 0;
+    Band b;
+    b.W = a.W; b.H = a.H; b.WW = a.WW; b.HC = a.HC;
+    b.rank = (CS > 1) ? (int)cluster.block_rank() : 0;
+    b.row0 = b.rank * b.HC;
+    b.nrows = max(0, min(b.HC, b.H - b.row0));
+    b.last_rank = (b.H - 1) / b.HC;  // last CTA that owns rows
+    b.last_mask = (b.W & 31) ? ((1u << (b.W & 31)) - 1u) : 0xffffffffu;
     const int frame = blockIdx.x / CS;
-    const int W = a.W, H = a.H, WW = a.WW, HC = a.HC;
-    const int row0 = rank * HC;
-    const int nrows = max(0, min(HC, H - row0));
-    // last CTA that owns rows
-    const int last_rank = (H - 1) / HC;
-    const uint32_t last_mask = (W & 31) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
+    const int WW = b.WW, nrows = b.nrows;
 
-    uint32_t* A = smem;                    // weak, later morphology ping-pong
-    uint32_t* B = smem + (HC + 2) * WW;    // edges
+    uint32_t* A = smem;                      // weak, later ping-pong
+    uint32_t* B = smem + (b.HC + 2) * WW;    // edges
 
-    const size_t plane = (size_t)frame * H * WW;
-    for (int i = threadIdx.x; i < (HC + 2) * WW; i += LNT) {
+    const size_t plane = (size_t)frame * b.H * WW;
+    for (int i = threadIdx.x; i < (b.HC + 2) * WW; i += LNT) {
         int r = i / WW - 1;  // local row index -1 .. HC
         uint32_t wv = 0, sv = 0;
         if (r >= 0 && r < nrows) {
-            wv = a.weak[plane + (size_t)(row0 + r) * WW + (i - (r + 1) * WW)];
-            sv = a.strong[plane + (size_t)(row0 + r) * WW + (i - (r + 1) * WW)];
+            wv = a.weak[plane + (size_t)(b.row0 + r) * WW + (i - (r + 1) * WW)];
+            sv = a.strong[plane + (size_t)(b.row0 + r) * WW + (i - (r + 1) * WW)];
         }
         A[i] = wv;
         B[i] = sv;
@@ -156,7 +206,7 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
     if (threadIdx.x < 16) (&s_flags[0][0])[threadIdx.x] = 0;
     __syncthreads();
 
-    // ---- hysteresis closure ----
+    // ---- hysteresis closure (in place, monotone: racing reads are benign) ----
     int parity = 0;
     for (;;) {
         for (;;) {
@@ -180,10 +230,10 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
         }
         if (CS == 1) break;
         cluster.sync();
-        int hc = pull_halo(cluster, B, WW, HC, nrows, rank, last_rank, nullptr, 0u);
+        int hc = pull_halo(cluster, B, b);
         hc = __syncthreads_or(hc);
         if (threadIdx.x < CS) {
-            int* remote = cluster.map_shared_rank(&s_flags[parity][rank], threadIdx.x);
+            int* remote = cluster.map_shared_rank(&s_flags[parity][b.rank], threadIdx.x);
             *remote = hc;
         }
         cluster.sync();
@@ -193,37 +243,69 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
         if (!any) break;
     }
 
-    if (a.canny_u8) store_u8(B, WW, W, row0, nrows, a.canny_u8 + (size_t)frame * W * H);
-    if (a.canny_bits)
-        for (int i = threadIdx.x; i < nrows * WW; i += LNT)
-            a.canny_bits[plane + (size_t)row0 * WW + i] = B[WW + i];
+    if (a.canny_u8) store_u8(B, b, a.canny_u8 + (size_t)frame * b.W * b.H);
+    if (a.canny_bits) store_bits(B, b, a.canny_bits + plane);
 
-    if (a.morph_u8 == nullptr && a.morph_bits == nullptr) return;  // uniform across the cluster
+    const bool want_morph = a.morph_u8 || a.morph_bits;
+    const bool want_mask = a.mask_u8 || a.mask_bits;
+    if (!want_morph && !want_mask) return;  // uniform across the cluster
 
-    // ---- dilate x2, erode x1 (ping-pong B -> A -> B -> A) ----
-    // halo rows of B are current (closure left them exchanged); image-border halos are 0.
-    __syncthreads();
-    morph3<true>(B, A, WW, nrows, last_mask);
-    if (CS > 1) { cluster.sync(); pull_halo(cluster, A, WW, HC, nrows, rank, last_rank, nullptr, 0u); }
-    else {
+    if (want_morph) {
+        // dilate x2, erode x1: B -> A -> B -> A (halo rows of B are current after the closure)
         __syncthreads();
-        for (int j = threadIdx.x; j < WW; j += LNT) { A[j] = 0u; A[(nrows + 1) * WW + j] = 0u; }
-    }
-    __syncthreads();
-    morph3<true>(A, B, WW, nrows, last_mask);
-    if (CS > 1) { cluster.sync(); pull_halo(cluster, B, WW, HC, nrows, rank, last_rank, nullptr, 0xffffffffu); }
-    else {
+        box3<true>(B, A, b);
+        refresh_halo(cluster, A, b, CS);
+        box3<true>(A, B, b);
+        refresh_halo(cluster, B, b, CS);
+        box3<false>(B, A, b);
         __syncthreads();
-        for (int j = threadIdx.x; j < WW; j += LNT) { B[j] = 0xffffffffu; B[(nrows + 1) * WW + j] = 0xffffffffu; }
+        if (a.morph_u8) store_u8(A, b, a.morph_u8 + (size_t)frame * b.W * b.H);
+        if (a.morph_bits) store_bits(A, b, a.morph_bits + plane);
     }
-    __syncthreads();
-    morph3<false>(B, A, WW, nrows, last_mask);
-    __syncthreads();
 
-    if (a.morph_u8) store_u8(A, WW, W, row0, nrows, a.morph_u8 + (size_t)frame * W * H);
-    if (a.morph_bits)
-        for (int i = threadIdx.x; i < nrows * WW; i += LNT)
-            a.morph_bits[plane + (size_t)row0 * WW + i] = A[WW + i];
+    if (want_mask) {
+        // the closure result was overwritten by the ping-pong: reload it (L2-resident) into B
+        if (CS > 1) cluster.sync();  // neighbours may still be pulling from B / A
+        __syncthreads();
+        if (want_morph)
+            for (int i = threadIdx.x; i < nrows * WW; i += LNT) B[WW + i] = a.canny_bits[plane + (size_t)b.row0 * WW + i];
+        refresh_halo(cluster, B, b, CS);
+        // t = NOT(cross-gradient(canny)) -> A
+        for (int i = threadIdx.x; i < nrows * WW; i += LNT) {
+            int lr = i / WW + 1, j = i - (lr - 1) * WW;
+            uint32_t dil = stencil<true, false>(B, b, lr, j), ero = stencil<false, false>(B, b, lr, j);
+            uint32_t t = ~(dil & ~ero);
+            if (j == WW - 1) t &= b.last_mask;
+            A[lr * WW + j] = t;
+        }
+        refresh_halo(cluster, A, b, CS);
+        // mask0 = canny | (t & ~cross-interior(t)) -> B (in place over canny: reads A and own word only)
+        for (int i = threadIdx.x; i < nrows * WW; i += LNT) {
+            int lr = i / WW + 1, j = i - (lr - 1) * WW;
+            uint32_t t = A[lr * WW + j];
+            // interior = t & up & down & left & right with 0 outside the image
+            uint32_t u = row_word(A, b, lr - 1, j, 0u), d = row_word(A, b, lr + 1, j, 0u);
+            uint32_t cl = row_word(A, b, lr, j - 1, 0u), cr = row_word(A, b, lr, j + 1, 0u);
+            uint32_t interior = t & u & d & ((t << 1) | (cl >> 31)) & ((t >> 1) | (cr << 31));
+            B[lr * WW + j] |= (t & ~interior);
+        }
+        // closes of 3, 4, 5 iterations then erode 3 (each k-iteration op == k passes of 3x3)
+        uint32_t* src = B;
+        uint32_t* dst = A;
+        auto pass = [&](bool is_or) {
+            refresh_halo(cluster, src, b, CS);
+            if (is_or) box3<true>(src, dst, b); else box3<false>(src, dst, b);
+            uint32_t* t = src; src = dst; dst = t;
+        };
+        for (int it = 0; it < 3; ++it) {
+            for (int k = 0; k < 3 + it; ++k) pass(true);
+            for (int k = 0; k < 3 + it; ++k) pass(false);
+        }
+        for (int k = 0; k < 3; ++k) pass(false);
+        __syncthreads();
+        if (a.mask_u8) store_u8(src, b, a.mask_u8 + (size_t)frame * b.W * b.H);
+        if (a.mask_bits) store_bits(src, b, a.mask_bits + plane);
+    }
     // keep this CTA's shared memory alive until every neighbour has finished pulling from it
     if (CS > 1) cluster.sync();
 }
@@ -231,10 +313,10 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
 }  // namespace
 
 int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_strong, int n, int w, int h,
-                     uint32_t* d_canny_bits, uint32_t* d_morph_bits, uint8_t* d_canny_u8, uint8_t* d_morph_u8)
+                     const EdgeOutputs& out)
 {
     const int WW = words_per_row(w);
-    // smallest cluster whose per-CTA planes fit in ~100 KB (two CTAs per SM), else up to 227 KB
+    // smallest cluster whose per-CTA planes fit in ~100 KB (two CTAs per SM), else up to 200 KB
     int cs = 1;
     size_t smem = 0;
     const size_t want = 100 * 1024, hard = 200 * 1024;
@@ -252,9 +334,10 @@ int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_st
     cs = chosen;
     LinkArgs a;
     a.weak = d_weak; a.strong = d_strong;
-    a.canny_bits = d_canny_bits; a.morph_bits = d_morph_bits;
-    a.canny_u8 = d_canny_u8; a.morph_u8 = d_morph_u8;
+    a.canny_bits = out.canny_bits; a.morph_bits = out.morph_bits; a.mask_bits = out.mask_bits;
+    a.canny_u8 = out.canny_u8; a.morph_u8 = out.morph_u8; a.mask_u8 = out.mask_u8;
     a.W = w; a.H = h; a.WW = WW; a.HC = (h + cs - 1) / cs;
+    if ((a.mask_bits || a.mask_u8) && !a.canny_bits) return MANTIS_ERR_INVALID;
     smem = (size_t)2 * (a.HC + 2) * WW * sizeof(uint32_t);
 
     MCHECK(c, cudaFuncSetAttribute(k_edge_link, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

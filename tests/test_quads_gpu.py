@@ -1,0 +1,65 @@
+"""GPU: edge mask and quad extraction (through the C ABI) against the oracle: mask bit-exact,
+contour / 4-gon counts equal, quad vertex lists equal in the reference's order, stretched test
+points bit-exact."""
+import numpy as np
+import pytest
+
+from cases import all_cases
+from frames import D_UNIT, K_GRID1, K_for, poses
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["grid1", "lena", "blocky_720x1280", "blocky_1080x1920", "odd_33x129", "ramps_480x640", "tiny_3x5",
+         "row_1x64", "col_70x1", "noise_123x77"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_mask_matches_oracle(ctx, name):
+    img = all_cases()[name]
+    mask = ctx.edge_mask(img)[0]
+    canny, _ = po.edge_stage(img, 50)
+    assert np.array_equal(mask, po.clean_mask(canny)), np.argwhere(mask != po.clean_mask(canny))[:5]
+
+
+def check_quads(fq, tr):
+    assert fq.flags == 0
+    assert (fq.n_contours, fq.n_quads_raw, fq.n_quads) == (tr.n_contours, tr.n_quads_raw, tr.n_quads)
+    for i in range(tr.n_quads):
+        assert list(fq.corners[i]) == list(tr.quad_corners[i]), i
+        assert list(fq.test_px[i]) == list(tr.quad_test_px[i]), i
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_quads_match_oracle(ctx, name):
+    img = all_cases()[name]
+    fq = ctx.quads(img)[0]
+    tr, _ = po.localize(img, K_GRID1, D_UNIT)
+    check_quads(fq, tr)
+
+
+def test_quads_synthetic_batch(ctx):
+    K, D = K_for(640, 480), np.zeros(4)
+    frames = np.stack([po.render_grid(R, t, K, D, 640, 480) for R, t in poses(12, seed=77)])
+    out = ctx.quads(frames)
+    total = 0
+    for i in range(len(frames)):
+        tr, _ = po.localize(frames[i], K, D)
+        check_quads(out[i], tr)
+        total += tr.n_quads
+    assert total > 100
+
+
+def test_quads_nested_and_thin_shapes(ctx):
+    """Islands in holes, 1-px lines shared by two borders, shapes touching the frame."""
+    img = np.zeros((120, 160, 3), np.uint8)
+    img[10:100, 10:150] = 255
+    img[25:85, 30:130] = 0
+    img[40:70, 50:110] = 200
+    img[50:60, 70:90] = 0
+    img[0:8, 0:40] = 255
+    img[110:120, 100:160] = 180
+    fq = ctx.quads(img)[0]
+    tr, _ = po.localize(img, K_for(160, 120), np.zeros(4))
+    check_quads(fq, tr)
+    assert tr.n_contours >= 6
