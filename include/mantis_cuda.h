@@ -125,6 +125,57 @@ typedef struct mantis_frame_quads {
 int mantis_quads_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height,
                        int stride_bytes, size_t frame_pitch_bytes, mantis_frame_quads* out, int mem);
 
+/*
+ * Whole-frame localization: everything quadDetection() does between receiving the image and
+ * calling publishPose() (src/mantis3.cpp:68-135).
+ */
+typedef struct mantis_frame {     /* one sensor_msgs/Image + CameraInfo of mantisService.srv:1-2 */
+    const uint8_t* bgr;           /* 8-bit BGR, HWC (host or device, see `mem`) */
+    int32_t width, height, stride_bytes;
+    float K[9];                   /* CameraInfo.K as the CV_32F 3x3 of get3x3FromVector, QuadDetection.h:189-201 */
+    double D[4];                  /* CameraInfo.D, fisheye coefficients (src/mantis3.cpp:74) */
+    double cam_to_base[7];        /* optional camera->base_link transform (x y z qx qy qz qw); identity if qw==0 */
+    uint64_t stamp_ns;
+    int32_t camera_id;
+} mantis_frame;
+
+enum { /* mantis_result.status */
+    MANTIS_FRAME_OK = 0,
+    MANTIS_FRAME_NO_QUADS = 1,       /* src/mantis3.cpp:83-84 early return */
+    MANTIS_FRAME_NO_HYPOTHESES = 2,  /* src/mantis3.cpp:94-97 early return */
+    MANTIS_FRAME_YAW_FAILED = 3,     /* determineBestYaw found no finite score (the reference calls back() on an empty vector) */
+    MANTIS_FRAME_OVERFLOW = 4        /* a capacity limit of the on-chip stages was hit (see MANTIS_FLAG_*) */
+};
+
+typedef struct mantis_result {    /* what publishPose() emits (PosePub.h:38-56) + the srv response fields */
+    double pos[3];                /* hyp.getPosition(): origin of W2C */
+    double quat_xyzw[4];          /* hyp.getQuaternion() */
+    double error;                 /* hyp.error (variance = error/600, PosePub.h:47); srv `weight` */
+    double min_yaw_diff;          /* publishPose gates on this > MINIMUM_YAW_DIFFERENCE (4000), PosePub.h:16 */
+    int32_t status;
+    int32_t n_quads;
+    int32_t n_hyps;               /* hypotheses kept by the rotation clustering */
+    int32_t n_particles;          /* hypotheses scored for this frame; srv `num_particles` */
+} mantis_result;
+
+typedef struct mantis_frame_trace { /* intermediate values, for parity tests */
+    int32_t n_contours, n_quads_raw, n_quads, flags;
+    int32_t n_hyps_generated, n_hyps_cluster, best_rot, pad_;
+    double first_best_error;      /* getBestNHypotheses(1) */
+    double optimized_error;       /* after optimizeHypothesisWithParticleFilter */
+    double optimized_w2c[12];     /* R row-major (9) + t (3) */
+    double shift_err[81];
+    double yaw_err[4];
+} mantis_frame_trace;
+
+/* World map (params/map.yaml): xyz triples, white first, then red, then green. */
+int mantis_set_map(mantis_ctx* ctx, const double* xyz, int n_white, int n_red, int n_green);
+
+/* frames[i].bgr lives where `mem` says; all frames of one call must share width/height/stride.
+ * out[n] (and the optional trace[n]) are host arrays. */
+int mantis_localize_batch(mantis_ctx* ctx, const mantis_frame* frames, int n, mantis_result* out,
+                          mantis_frame_trace* trace, int mem);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,7 +11,10 @@ from .binding import (  # noqa: F401
     MEM_HOST,
     Config,
     Context,
+    Frame,
     FrameQuads,
+    FrameTrace,
+    Result,
     MantisError,
     build_library,
     library_path,

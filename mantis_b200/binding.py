@@ -54,6 +54,32 @@ class FrameQuads(ctypes.Structure):
                 ("test_px", (ctypes.c_double * 8) * MAX_QUADS)]
 
 
+class Frame(ctypes.Structure):
+    """mantis_frame: one Image + CameraInfo of mantisService.srv."""
+
+    _fields_ = [("bgr", ctypes.c_void_p), ("width", ctypes.c_int32), ("height", ctypes.c_int32),
+                ("stride_bytes", ctypes.c_int32), ("K", ctypes.c_float * 9), ("D", ctypes.c_double * 4),
+                ("cam_to_base", ctypes.c_double * 7), ("stamp_ns", ctypes.c_uint64), ("camera_id", ctypes.c_int32)]
+
+
+class Result(ctypes.Structure):
+    """mantis_result: pose + error/weight + counts (PosePub.h:38-56, mantisService.srv:9-12)."""
+
+    _fields_ = [("pos", ctypes.c_double * 3), ("quat_xyzw", ctypes.c_double * 4), ("error", ctypes.c_double),
+                ("min_yaw_diff", ctypes.c_double), ("status", ctypes.c_int32), ("n_quads", ctypes.c_int32),
+                ("n_hyps", ctypes.c_int32), ("n_particles", ctypes.c_int32)]
+
+
+class FrameTrace(ctypes.Structure):
+    """mantis_frame_trace."""
+
+    _fields_ = [("n_contours", ctypes.c_int32), ("n_quads_raw", ctypes.c_int32), ("n_quads", ctypes.c_int32),
+                ("flags", ctypes.c_int32), ("n_hyps_generated", ctypes.c_int32), ("n_hyps_cluster", ctypes.c_int32),
+                ("best_rot", ctypes.c_int32), ("pad_", ctypes.c_int32), ("first_best_error", ctypes.c_double),
+                ("optimized_error", ctypes.c_double), ("optimized_w2c", ctypes.c_double * 12),
+                ("shift_err", ctypes.c_double * 81), ("yaw_err", ctypes.c_double * 4)]
+
+
 def library_path():
     return os.path.join(_HERE, "libmantis_cuda.so")
 
@@ -97,6 +123,8 @@ def load_library():
                                       c.c_void_p, c.c_int]
     lib.mantis_quads_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
                                        c.c_void_p, c.c_int]
+    lib.mantis_set_map.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int]
+    lib.mantis_localize_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
     _LIB = lib
     return lib
 
@@ -203,3 +231,41 @@ class Context:
         rc = self._lib.mantis_quads_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, ctypes.addressof(out), MEM_HOST)
         self._check(rc, "mantis_quads_batch")
         return out
+
+    # -- quadDetection(), src/mantis3.cpp:68-135 --
+    def set_map(self, white, red, green):
+        xyz = np.ascontiguousarray(np.concatenate([white, red, green]), np.float64)
+        rc = self._lib.mantis_set_map(self._h, _ptr(xyz), len(white), len(red), len(green))
+        self._check(rc, "mantis_set_map")
+
+    def make_frames(self, ptrs, w, h, K, D, stride=None):
+        """Array of mantis_frame for buffers (host arrays or device pointers) sharing K / D."""
+        n = len(ptrs)
+        fr = (Frame * n)()
+        Kf = np.ascontiguousarray(K, np.float32).reshape(-1)
+        Dd = np.ascontiguousarray(D, np.float64).reshape(-1)
+        for i, p in enumerate(ptrs):
+            fr[i].bgr = p if isinstance(p, int) else p.ctypes.data
+            fr[i].width, fr[i].height, fr[i].stride_bytes = w, h, (3 * w if stride is None else stride)
+            fr[i].K[:] = Kf.tolist()
+            fr[i].D[:] = Dd.tolist()
+            fr[i].camera_id = 0
+        return fr
+
+    def localize(self, bgr, K, D, want_trace=False):
+        """bgr: uint8 [n, H, W, 3] on the host, one camera model for all.  Returns (results, traces)."""
+        bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, _ = bgr.shape
+        frames = self.make_frames([bgr[i] for i in range(n)], w, h, K, D)
+        return self.localize_frames(frames, MEM_HOST, want_trace)
+
+    def localize_frames(self, frames, mem, want_trace=False):
+        n = len(frames)
+        out = (Result * n)()
+        tr = (FrameTrace * n)() if want_trace else None
+        rc = self._lib.mantis_localize_batch(self._h, ctypes.addressof(frames), n, ctypes.addressof(out),
+                                             ctypes.addressof(tr) if want_trace else None, mem)
+        self._check(rc, "mantis_localize_batch")
+        return out, tr

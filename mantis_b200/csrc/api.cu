@@ -3,6 +3,8 @@
 #include <new>
 #include "ctx.h"
 
+int ctx_init_tables(mantis_ctx* c);
+
 extern "C" {
 
 void mantis_default_config(mantis_config* cfg)
@@ -56,6 +58,11 @@ int mantis_create(const mantis_config* cfg, int device, mantis_ctx** out)
         delete c;
         return MANTIS_ERR_CUDA;
     }
+    int rc = ctx_init_tables(c);
+    if (rc != MANTIS_OK) {
+        mantis_destroy(c);
+        return rc;
+    }
     *out = c;
     return MANTIS_OK;
 }
@@ -66,7 +73,9 @@ int mantis_destroy(mantis_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_out0,
-                      &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->frame_quads};
+                      &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->frame_quads,
+                      &c->cams, &c->hyps, &c->sel, &c->pose_info, &c->results, &c->traces, &c->mask_bits,
+                      &c->d_map, &c->d_rand, &c->d_shifts};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->pin_in) cudaFreeHost(c->pin_in);

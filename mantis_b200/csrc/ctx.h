@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 #include "../../include/mantis_cuda.h"
+#include "pipeline.cuh"
 
 struct DevBuf {
     void* p = nullptr;
@@ -24,6 +25,10 @@ struct mantis_ctx {
     DevBuf canny_bits, morph_bits;  // bit-packed results of the per-frame kernel
     DevBuf q_pts, q_dst, q_stack, q_owner;   // quad kernel scratch (per resident CTA)
     DevBuf frame_quads;                      // FrameQuads[n]
+    DevBuf cams, hyps, sel, pose_info, results, traces, mask_bits;  // localize scratch (per chunk)
+    DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts
+    int n_map = 0, n_green = 0, n_shift = 0;
+    Tf rotz;                                 // +90 degrees about z
     DevBuf stage_in, stage_out0, stage_out1;  // device staging for MANTIS_MEM_HOST callers
     void* pin_in = nullptr;  size_t pin_in_cap = 0;   // pinned host staging
     void* pin_out = nullptr; size_t pin_out_cap = 0;
@@ -75,5 +80,14 @@ int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_st
 
 // Contours -> approxPolyDP -> 4-gons -> de-duplicated quads, per frame, in OpenCV's order.
 int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int h, mantis_frame_quads* d_out);
+
+namespace pm { struct Camera; }
+int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_cams, int n, Hyp* d_hyps, short* d_sel,
+                FramePose* d_info);
+int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n,
+                  int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
+                  const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace);
+extern "C" int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int height, int stride_bytes,
+                   size_t frame_pitch_bytes, const EdgeOutputs& out);
 
 static inline int words_per_row(int w) { return (w + 31) >> 5; }

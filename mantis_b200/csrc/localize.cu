@@ -1,0 +1,175 @@
+// localize.cu -- mantis_localize_batch(): the whole quadDetection() callback (src/mantis3.cpp:68-135)
+// for a batch of frames, plus the per-context tables it needs (world map, refinement
+// perturbations, cell shifts).
+#include <new>
+#include <vector>
+#include "ctx.h"
+#include "cvrng.h"
+#include "posemath.cuh"
+
+static int upload(mantis_ctx* c, DevBuf& b, const void* src, size_t bytes)
+{
+    int rc = ctx_reserve(c, b, bytes ? bytes : 1);
+    if (rc) return rc;
+    if (bytes) MCHECK(c, cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+    MCHECK(c, cudaStreamSynchronize(c->stream));
+    return MANTIS_OK;
+}
+
+// The map of params/map.yaml, as params/matGen_dense.m prints it ("%f") and
+// parseCoordinatesFromString (Mantis3Params.h:125-152) reads it back (atof).
+static double yaml_value(double v)
+{
+    char buf[64];
+    snprintf(buf, sizeof(buf), "%f", v);
+    return atof(buf);
+}
+
+static void default_map(double spacing, std::vector<double>& xyz, int& nw, int& nr, int& ng)
+{
+    auto push = [&](double x, double y) { xyz.push_back(yaml_value(x)); xyz.push_back(yaml_value(y)); xyz.push_back(0.0); };
+    nw = nr = ng = 0;
+    for (int iy = 0; iy < 8; ++iy)                       // 8 inner x-lines, 37 points each
+        for (int ix = 0; ix < 37; ++ix) { push(spacing * (-4.5 + 0.25 * ix), spacing * (-3.5 + iy)); ++nw; }
+    for (int ix = 0; ix < 10; ++ix)                      // 10 y-lines, 35 points each
+        for (int iy = 0; iy < 35; ++iy) { push(spacing * (-4.5 + ix), spacing * (-4.25 + 0.25 * iy)); ++nw; }
+    for (int ix = 0; ix < 37; ++ix) { push(spacing * (-4.5 + 0.25 * ix), -4.5 * spacing); ++nr; }  // red edge
+    for (int ix = 0; ix < 37; ++ix) { push(spacing * (-4.5 + 0.25 * ix), 4.5 * spacing); ++ng; }   // green edge
+}
+
+int ctx_init_tables(mantis_ctx* c)
+{
+    // +90 degrees about z: tf::Transform(tf::Quaternion(0, 0, 1/sqrt(2), 1/sqrt(2)))
+    double q[4] = {0, 0, 1 / sqrt(2.0), 1 / sqrt(2.0)};
+    pm::quat_to_mat(q, c->rotz.R);
+    c->rotz.t[0] = c->rotz.t[1] = c->rotz.t[2] = 0;
+
+    // generateRandomHypothesis (PoseAdjustment.h:13-23) for every (iteration, particle), in draw
+    // order; argument lists evaluated right to left (GCC, x86-64): yaw, pitch, roll, then z, y, x.
+    const int total = c->cfg.iterations * c->cfg.particles;
+    std::vector<Tf> rnd((size_t)(total > 0 ? total : 1));
+    CvRng rng(c->cfg.rng_seed);
+    for (int i = 0; i < total; ++i) {
+        double yaw = rng.gaussian(c->cfg.rot_sigma), pitch = rng.gaussian(c->cfg.rot_sigma), roll = rng.gaussian(c->cfg.rot_sigma);
+        double z = rng.gaussian(c->cfg.trans_sigma), y = rng.gaussian(c->cfg.trans_sigma), x = rng.gaussian(c->cfg.trans_sigma);
+        pm::set_rpy(roll, pitch, yaw, rnd[i].R);
+        rnd[i].t[0] = x; rnd[i].t[1] = y; rnd[i].t[2] = z;
+    }
+    int rc = upload(c, c->d_rand, rnd.data(), sizeof(Tf) * (size_t)total);
+    if (rc) return rc;
+
+    // computeAllShiftedHypothesesFAST (HypothesisGeneration.h:125-140): the loop variables are
+    // accumulated in double exactly as written
+    std::vector<double> sh;
+    const double gs = c->cfg.grid_spacing, half = ((double)c->cfg.grid_size / 2.0) * gs;
+    for (double x = -half + gs / 2.0; x < half; x += gs)
+        for (double y = -half + gs / 2.0; y < half; y += gs) { sh.push_back(x); sh.push_back(y); }
+    c->n_shift = (int)(sh.size() / 2);
+    if ((rc = upload(c, c->d_shifts, sh.data(), sizeof(double) * sh.size()))) return rc;
+
+    std::vector<double> xyz;
+    int nw, nr, ng;
+    default_map(c->cfg.grid_spacing, xyz, nw, nr, ng);
+    return mantis_set_map(c, xyz.data(), nw, nr, ng);
+}
+
+extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int n_red, int n_green)
+{
+    if (!c || !xyz || n_white < 0 || n_red < 0 || n_green < 0) return MANTIS_ERR_INVALID;
+    const int n = n_white + n_red + n_green;
+    if (n <= 0 || n > 1024 || n_green > 40) return MANTIS_ERR_INVALID;
+    MCHECK(c, cudaSetDevice(c->device));
+    int rc = upload(c, c->d_map, xyz, sizeof(double) * 3 * (size_t)n);
+    if (rc) return rc;
+    c->n_map = n;
+    c->n_green = n_green;
+    return MANTIS_OK;
+}
+
+extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, int n, mantis_result* out,
+                                     mantis_frame_trace* trace, int mem)
+{
+    if (!c || n < 0 || (n > 0 && (!frames || !out)) || (mem != MANTIS_MEM_HOST && mem != MANTIS_MEM_DEVICE))
+        return MANTIS_ERR_INVALID;
+    if (n == 0) return MANTIS_OK;
+    const int W = frames[0].width, H = frames[0].height, stride0 = frames[0].stride_bytes;
+    if (W <= 0 || H <= 0 || W > 32767 || H > 32767 || stride0 < 3 * W) return MANTIS_ERR_INVALID;
+    for (int i = 0; i < n; ++i)
+        if (!frames[i].bgr || frames[i].width != W || frames[i].height != H || frames[i].stride_bytes != stride0)
+            return MANTIS_ERR_INVALID;
+    size_t dev_pitch = (size_t)stride0 * H;
+    if (mem == MANTIS_MEM_DEVICE && n > 1) {
+        dev_pitch = (size_t)(frames[1].bgr - frames[0].bgr);
+        for (int i = 1; i < n; ++i)
+            if (frames[i].bgr != frames[0].bgr + (size_t)i * dev_pitch) {
+                snprintf(c->err, sizeof(c->err), "device-resident frames of one call must be equally spaced");
+                return MANTIS_ERR_INVALID;
+            }
+    }
+    MCHECK(c, cudaSetDevice(c->device));
+
+    const int CHUNK = 512;
+    const int WW = words_per_row(W);
+    const int nc_max = n < CHUNK ? n : CHUNK;
+    const size_t plane_bytes = (size_t)nc_max * H * WW * sizeof(uint32_t);
+    int rc;
+    if ((rc = ctx_reserve(c, c->canny_bits, plane_bytes)) || (rc = ctx_reserve(c, c->morph_bits, plane_bytes)) ||
+        (rc = ctx_reserve(c, c->mask_bits, plane_bytes)) ||
+        (rc = ctx_reserve(c, c->frame_quads, (size_t)nc_max * sizeof(FrameQuads))) ||
+        (rc = ctx_reserve(c, c->cams, (size_t)nc_max * sizeof(pm::Camera))) ||
+        (rc = ctx_reserve(c, c->hyps, (size_t)nc_max * MANTIS_MAX_HYPS * sizeof(Hyp))) ||
+        (rc = ctx_reserve(c, c->sel, (size_t)nc_max * MANTIS_MAX_HYPS * sizeof(short))) ||
+        (rc = ctx_reserve(c, c->pose_info, (size_t)nc_max * sizeof(FramePose))) ||
+        (rc = ctx_reserve(c, c->results, (size_t)nc_max * sizeof(mantis_result))) ||
+        (rc = ctx_reserve(c, c->traces, (size_t)nc_max * sizeof(mantis_frame_trace))))
+        return rc;
+    if (mem == MANTIS_MEM_HOST && (rc = ctx_reserve(c, c->stage_in, (size_t)nc_max * 3 * W * H))) return rc;
+
+    std::vector<pm::Camera> cams((size_t)nc_max);
+    for (int f0 = 0; f0 < n; f0 += CHUNK) {
+        const int nc = (n - f0 < CHUNK) ? (n - f0) : CHUNK;
+        const uint8_t* d_in;
+        size_t pitch;
+        int stride;
+        if (mem == MANTIS_MEM_HOST) {  // gather into a tightly packed device batch
+            stride = 3 * W;
+            pitch = (size_t)stride * H;
+            for (int i = 0; i < nc; ++i)
+                MCHECK(c, cudaMemcpy2DAsync((uint8_t*)c->stage_in.p + (size_t)i * pitch, stride, frames[f0 + i].bgr, stride0,
+                                            (size_t)3 * W, H, cudaMemcpyHostToDevice, c->stream));
+            d_in = (const uint8_t*)c->stage_in.p;
+        } else {
+            stride = stride0;
+            pitch = dev_pitch;
+            d_in = frames[f0].bgr;
+        }
+        for (int i = 0; i < nc; ++i) {
+            const mantis_frame& f = frames[f0 + i];
+            pm::Camera& cm = cams[i];
+            cm.fx = (double)f.K[0]; cm.fy = (double)f.K[4]; cm.cx = (double)f.K[2]; cm.cy = (double)f.K[5];
+            for (int k = 0; k < 4; ++k) cm.D[k] = f.D[k];
+        }
+        MCHECK(c, cudaMemcpyAsync(c->cams.p, cams.data(), sizeof(pm::Camera) * (size_t)nc, cudaMemcpyHostToDevice, c->stream));
+
+        EdgeOutputs eo;
+        eo.canny_bits = (uint32_t*)c->canny_bits.p;
+        eo.morph_bits = (uint32_t*)c->morph_bits.p;
+        eo.mask_bits = (uint32_t*)c->mask_bits.p;
+        if ((rc = run_edge_stage(c, d_in, nc, W, H, stride, pitch, eo))) return rc;
+        if ((rc = launch_quads(c, eo.morph_bits, nc, W, H, (FrameQuads*)c->frame_quads.p))) return rc;
+        if ((rc = launch_pose(c, (const FrameQuads*)c->frame_quads.p, (const pm::Camera*)c->cams.p, nc, (Hyp*)c->hyps.p,
+                              (short*)c->sel.p, (FramePose*)c->pose_info.p)))
+            return rc;
+        if ((rc = launch_search(c, d_in, pitch, stride, eo.mask_bits, nc, W, H, (const pm::Camera*)c->cams.p,
+                                (const FrameQuads*)c->frame_quads.p, (const Hyp*)c->hyps.p, (const short*)c->sel.p,
+                                (const FramePose*)c->pose_info.p, (mantis_result*)c->results.p,
+                                trace ? (mantis_frame_trace*)c->traces.p : nullptr)))
+            return rc;
+        MCHECK(c, cudaMemcpyAsync(out + f0, c->results.p, sizeof(mantis_result) * (size_t)nc, cudaMemcpyDeviceToHost, c->stream));
+        if (trace)
+            MCHECK(c, cudaMemcpyAsync(trace + f0, c->traces.p, sizeof(mantis_frame_trace) * (size_t)nc,
+                                      cudaMemcpyDeviceToHost, c->stream));
+        MCHECK(c, cudaStreamSynchronize(c->stream));
+    }
+    return MANTIS_OK;
+}

@@ -28,3 +28,10 @@ struct Hyp {
     double q[4];
     double error;
 };
+
+// Per-frame by-products of the pose kernel (also surfaced through mantis_frame_trace).
+struct FramePose {
+    int n_hyps_generated, n_sel;
+    int quad_pass[MANTIS_MAX_QUADS];
+    double quad_img_err[MANTIS_MAX_QUADS];
+};
