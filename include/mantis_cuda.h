@@ -80,6 +80,16 @@ uint64_t mantis_launch_count(const mantis_ctx* ctx);
 void* mantis_stream(const mantis_ctx* ctx);
 
 /*
+ * Per-stage device timing of mantis_localize_batch (CUDA events on the context stream).
+ * Stages: 0 input staging (H2D), 1 candidate kernel (gray/blur/Sobel/NMS), 2 edge-link kernel
+ * (hysteresis, morphology, mask), 3 quad kernel, 4 pose kernel, 5 search kernel, 6 result D2H.
+ */
+#define MANTIS_N_STAGES 7
+int mantis_set_profiling(mantis_ctx* ctx, int enabled);
+/* Copies the accumulated milliseconds per stage into ms[MANTIS_N_STAGES] and resets them. */
+int mantis_get_stage_ms(mantis_ctx* ctx, double* ms);
+
+/*
  * Image stage of detectQuadrilaterals(): cvtColor(BGR2GRAY) -> GaussianBlur(3x3, s=3)
  * -> Canny(T, 3T, 3) -> dilate x2 -> erode x1   (include/mantis3/QuadDetection.h:209-214;
  * the first three are repeated verbatim by cleanImageByEdge, HypothesisEvaluation.h:323-327).
@@ -175,6 +185,19 @@ int mantis_set_map(mantis_ctx* ctx, const double* xyz, int n_white, int n_red, i
  * out[n] (and the optional trace[n]) are host arrays. */
 int mantis_localize_batch(mantis_ctx* ctx, const mantis_frame* frames, int n, mantis_result* out,
                           mantis_frame_trace* trace, int mem);
+
+/*
+ * Synthetic frame source on the device: the floor grid of params/map.yaml ray-cast through the
+ * fisheye model for n camera poses (stands in for GridRenderer::renderGrid,
+ * include/mantis3/GridRenderer.cpp:292-353, whose OpenGL path cannot run here).
+ *   poses_w2c   host array, per frame 12 doubles: R (row-major, camera->world) then t (camera origin)
+ *   d_bgr_out   DEVICE buffer receiving n frames of 8-bit BGR
+ *   noise_sigma > 0 adds N(0, sigma) per channel from a counter-based hash of (seed, frame, pixel)
+ */
+int mantis_render_grid_batch(mantis_ctx* ctx, const double* poses_w2c, int n, int width, int height,
+                             const float* K, const double* D, double line_width, int floor_level,
+                             float noise_sigma, uint32_t seed, uint8_t* d_bgr_out, int stride_bytes,
+                             size_t frame_pitch_bytes);
 
 #ifdef __cplusplus
 }

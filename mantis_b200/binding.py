@@ -125,6 +125,11 @@ def load_library():
                                        c.c_void_p, c.c_int]
     lib.mantis_set_map.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int]
     lib.mantis_localize_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_render_grid_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p,
+                                             c.c_void_p, c.c_double, c.c_int, c.c_float, c.c_uint32, c.c_void_p,
+                                             c.c_int, c.c_size_t]
+    lib.mantis_set_profiling.argtypes = [c.c_void_p, c.c_int]
+    lib.mantis_get_stage_ms.argtypes = [c.c_void_p, c.c_void_p]
     _LIB = lib
     return lib
 
@@ -269,3 +274,26 @@ class Context:
                                              ctypes.addressof(tr) if want_trace else None, mem)
         self._check(rc, "mantis_localize_batch")
         return out, tr
+
+    # -- synthetic frame source (stands in for GridRenderer.cpp:292-353) --
+    def render_grid_device(self, poses, w, h, K, D, d_out, line_width=0.04, floor_level=30, noise_sigma=0.0, seed=0):
+        """poses: list of (R_w2c[3,3], t_w2c[3]); d_out: device pointer to n*h*w*3 bytes."""
+        flat = np.ascontiguousarray([np.concatenate([np.asarray(R, np.float64).reshape(-1), np.asarray(t, np.float64)])
+                                     for R, t in poses], np.float64)
+        Kf = np.ascontiguousarray(K, np.float32)
+        Dd = np.ascontiguousarray(D, np.float64)
+        rc = self._lib.mantis_render_grid_batch(self._h, _ptr(flat), len(poses), w, h, _ptr(Kf), _ptr(Dd),
+                                                float(line_width), int(floor_level), float(noise_sigma), int(seed),
+                                                _ptr(d_out), 3 * w, 3 * w * h)
+        self._check(rc, "mantis_render_grid_batch")
+
+    STAGES = ("h2d", "edge_candidates", "edge_link", "quads", "pose", "search", "d2h")
+
+    def set_profiling(self, enabled=True):
+        self._check(self._lib.mantis_set_profiling(self._h, int(enabled)), "mantis_set_profiling")
+
+    def stage_ms(self):
+        """Accumulated device milliseconds per stage since the last call (dict)."""
+        ms = (ctypes.c_double * 7)()
+        self._check(self._lib.mantis_get_stage_ms(self._h, ms), "mantis_get_stage_ms")
+        return dict(zip(self.STAGES, list(ms)))

@@ -75,13 +75,49 @@ int mantis_destroy(mantis_ctx* c)
     DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_out0,
                       &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->frame_quads,
                       &c->cams, &c->hyps, &c->sel, &c->pose_info, &c->results, &c->traces, &c->mask_bits,
-                      &c->d_map, &c->d_rand, &c->d_shifts};
+                      &c->d_map, &c->d_rand, &c->d_shifts, &c->render_poses, &c->quad_hyp, &c->pose_offs};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->pin_in) cudaFreeHost(c->pin_in);
     if (c->pin_out) cudaFreeHost(c->pin_out);
+    for (int i = 0; i <= MANTIS_N_STAGES; ++i)
+        if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     cudaStreamDestroy(c->stream);
     delete c;
+    return MANTIS_OK;
+}
+
+// Tuning aid (not part of the public header): accumulated clock64 deltas of the quad kernel's phases.
+int mantis_debug_clocks(mantis_ctx* c, long long* out8)
+{
+    if (!c) return MANTIS_ERR_INVALID;
+    MCHECK(c, cudaSetDevice(c->device));
+    if (!c->dbg_clocks) {
+        MCHECK(c, cudaMalloc(&c->dbg_clocks, 8 * sizeof(long long)));
+        MCHECK(c, cudaMemset(c->dbg_clocks, 0, 8 * sizeof(long long)));
+    }
+    if (out8) {
+        MCHECK(c, cudaMemcpy(out8, c->dbg_clocks, 8 * sizeof(long long), cudaMemcpyDeviceToHost));
+        MCHECK(c, cudaMemset(c->dbg_clocks, 0, 8 * sizeof(long long)));
+    }
+    return MANTIS_OK;
+}
+
+int mantis_set_profiling(mantis_ctx* c, int enabled)
+{
+    if (!c) return MANTIS_ERR_INVALID;
+    MCHECK(c, cudaSetDevice(c->device));
+    if (enabled && !c->ev[0])
+        for (int i = 0; i <= MANTIS_N_STAGES; ++i) MCHECK(c, cudaEventCreate(&c->ev[i]));
+    c->profiling = enabled != 0;
+    for (int i = 0; i < MANTIS_N_STAGES; ++i) c->stage_ms[i] = 0;
+    return MANTIS_OK;
+}
+
+int mantis_get_stage_ms(mantis_ctx* c, double* ms)
+{
+    if (!c || !ms) return MANTIS_ERR_INVALID;
+    for (int i = 0; i < MANTIS_N_STAGES; ++i) { ms[i] = c->stage_ms[i]; c->stage_ms[i] = 0; }
     return MANTIS_OK;
 }
 
@@ -133,6 +169,7 @@ int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int hei
                                          frame_pitch_bytes, low, high, (uint32_t*)c->weak.p + poff,
                                          (uint32_t*)c->strong.p + poff)))
             return rc;
+        prof_mark(c, 2);
         EdgeOutputs eo;
         eo.canny_bits = out.canny_bits ? out.canny_bits + poff : nullptr;
         eo.morph_bits = out.morph_bits ? out.morph_bits + poff : nullptr;

@@ -20,12 +20,20 @@ struct mantis_ctx {
     uint64_t launches = 0;
     char err[256] = {0};
 
+    // optional per-stage timing (CUDA events on the context stream)
+    void* dbg_clocks = nullptr;  // device array of 8 long long, set by mantis_debug_clocks
+    bool profiling = false;
+    cudaEvent_t ev[MANTIS_N_STAGES + 1] = {};
+    double stage_ms[MANTIS_N_STAGES] = {};
+
     // scratch (grows monotonically)
     DevBuf weak, strong;      // bit planes from the candidate kernel
     DevBuf canny_bits, morph_bits;  // bit-packed results of the per-frame kernel
     DevBuf q_pts, q_dst, q_stack, q_owner;   // quad kernel scratch (per resident CTA)
     DevBuf frame_quads;                      // FrameQuads[n]
+    DevBuf quad_hyp, pose_offs;
     DevBuf cams, hyps, sel, pose_info, results, traces, mask_bits;  // localize scratch (per chunk)
+    DevBuf render_poses;
     DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts
     int n_map = 0, n_green = 0, n_shift = 0;
     Tf rotz;                                 // +90 degrees about z
@@ -43,6 +51,20 @@ struct mantis_ctx {
             return MANTIS_ERR_CUDA;                                                        \
         }                                                                                  \
     } while (0)
+
+// stage timing helpers: mark(i) records the event that ends stage i-1 / starts stage i
+inline void prof_mark(mantis_ctx* c, int i)
+{
+    if (c->profiling) cudaEventRecord(c->ev[i], c->stream);
+}
+inline void prof_collect(mantis_ctx* c, int first, int last)  // after a stream sync
+{
+    if (!c->profiling) return;
+    for (int i = first; i < last; ++i) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, c->ev[i], c->ev[i + 1]) == cudaSuccess) c->stage_ms[i] += ms;
+    }
+}
 
 inline int ctx_reserve(mantis_ctx* c, DevBuf& b, size_t bytes)
 {

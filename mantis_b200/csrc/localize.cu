@@ -131,6 +131,7 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         const uint8_t* d_in;
         size_t pitch;
         int stride;
+        prof_mark(c, 0);
         if (mem == MANTIS_MEM_HOST) {  // gather into a tightly packed device batch
             stride = 3 * W;
             pitch = (size_t)stride * H;
@@ -151,25 +152,32 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         }
         MCHECK(c, cudaMemcpyAsync(c->cams.p, cams.data(), sizeof(pm::Camera) * (size_t)nc, cudaMemcpyHostToDevice, c->stream));
 
+        prof_mark(c, 1);
         EdgeOutputs eo;
         eo.canny_bits = (uint32_t*)c->canny_bits.p;
         eo.morph_bits = (uint32_t*)c->morph_bits.p;
         eo.mask_bits = (uint32_t*)c->mask_bits.p;
         if ((rc = run_edge_stage(c, d_in, nc, W, H, stride, pitch, eo))) return rc;
+        prof_mark(c, 3);
         if ((rc = launch_quads(c, eo.morph_bits, nc, W, H, (FrameQuads*)c->frame_quads.p))) return rc;
+        prof_mark(c, 4);
         if ((rc = launch_pose(c, (const FrameQuads*)c->frame_quads.p, (const pm::Camera*)c->cams.p, nc, (Hyp*)c->hyps.p,
                               (short*)c->sel.p, (FramePose*)c->pose_info.p)))
             return rc;
+        prof_mark(c, 5);
         if ((rc = launch_search(c, d_in, pitch, stride, eo.mask_bits, nc, W, H, (const pm::Camera*)c->cams.p,
                                 (const FrameQuads*)c->frame_quads.p, (const Hyp*)c->hyps.p, (const short*)c->sel.p,
                                 (const FramePose*)c->pose_info.p, (mantis_result*)c->results.p,
                                 trace ? (mantis_frame_trace*)c->traces.p : nullptr)))
             return rc;
+        prof_mark(c, 6);
         MCHECK(c, cudaMemcpyAsync(out + f0, c->results.p, sizeof(mantis_result) * (size_t)nc, cudaMemcpyDeviceToHost, c->stream));
         if (trace)
             MCHECK(c, cudaMemcpyAsync(trace + f0, c->traces.p, sizeof(mantis_frame_trace) * (size_t)nc,
                                       cudaMemcpyDeviceToHost, c->stream));
+        prof_mark(c, 7);
         MCHECK(c, cudaStreamSynchronize(c->stream));
+        prof_collect(c, 0, MANTIS_N_STAGES);
     }
     return MANTIS_OK;
 }

@@ -14,6 +14,7 @@ struct QuadArgs {
     short2* pts; short2* dst; int2* stack; uint16_t* owner;  // slot-strided scratch
     FrameQuads* out;
     double eps, stretch, radius_mult;
+    long long* phase_clocks;  // optional: 8 accumulated clock64 deltas (debug / tuning)
 };
 
 __device__ __forceinline__ uint32_t bits_at(const uint32_t* p, int WW, int H, int y, int j)
@@ -74,6 +75,8 @@ __global__ void __launch_bounds__(QNT) k_quads(QuadArgs a)
             s_unp[k] = np;
         };
 
+        long long t_prev = clock64();
+        auto lap = [&](int k) { if (a.phase_clocks && tid == 0) { long long t = clock64(); atomicAdd((unsigned long long*)&a.phase_clocks[k], (unsigned long long)(t - t_prev)); t_prev = t; } };
         // 1. candidates (whole words at a time)
         for (int i = tid; i < H * WW; i += QNT) {
             int y = i / WW, j = i - y * WW;
@@ -98,12 +101,14 @@ __global__ void __launch_bounds__(QNT) k_quads(QuadArgs a)
             }
         }
         __syncthreads();
+        lap(0);
         // 2. probe walks
         {
             int nc = min(s_ncand, MAXCAND);
             for (int i = tid; i < nc; i += QNT) try_candidate(s_cand[i]);
         }
         __syncthreads();
+        lap(1);
         const int nb = min(s_nstart, MAXB);
         // 3. discovery order (rank by counting) and point offsets
         for (int i = tid; i < nb; i += QNT) {
@@ -120,6 +125,7 @@ __global__ void __launch_bounds__(QNT) k_quads(QuadArgs a)
             if (acc > MANTIS_MAX_PTS) s_flags |= FRAME_FLAG_POINT_OVERFLOW;
         }
         __syncthreads();
+        lap(2);
         const bool overflow = s_flags != 0;
         int nraw = 0;
         if (!overflow) {
@@ -132,6 +138,7 @@ __global__ void __launch_bounds__(QNT) k_quads(QuadArgs a)
                 follow_border(im, is_hole ? x - 1 : x, y, is_hole, v);
             }
             __syncthreads();
+            lap(3);
             // 5. approxPolyDP, 6. hole -> outer border
             for (int b = tid; b < nb; b += QNT) {
                 int n4 = approx_poly_closed(pts + s_off[b], s_np[b], a.eps, dst + s_off[b], stack + s_off[b] + 2 * b);
@@ -148,6 +155,7 @@ __global__ void __launch_bounds__(QNT) k_quads(QuadArgs a)
                 s_parent[b] = (short)cur;
             }
             __syncthreads();
+            lap(4);
             // 7. CCOMP output order: outers by descending rank, each followed by its holes, descending
             for (int b = tid; b < nb; b += QNT) {
                 bool hole_b = s_key[b] & 1u;
@@ -167,6 +175,7 @@ __global__ void __launch_bounds__(QNT) k_quads(QuadArgs a)
             }
             __syncthreads();
         }
+        lap(5);
         // 8. quads: constructor, de-duplication, output (sequential, tiny)
         if (tid == 0) {
             out->n_contours = nb;
@@ -234,6 +243,7 @@ __global__ void __launch_bounds__(QNT) k_quads(QuadArgs a)
                 out->n_quads = 0;
             }
         }
+        lap(6);
     }
 }
 
@@ -257,6 +267,7 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     a.eps = (double)c->cfg.polygon_epsilon;
     a.stretch = c->cfg.quad_stretch_factor;
     a.radius_mult = c->cfg.search_radius_multiplier;
+    a.phase_clocks = (long long*)c->dbg_clocks;
     k_quads<<<slots, QNT, 0, c->stream>>>(a);
     c->launches++;
     MCHECK(c, cudaGetLastError());

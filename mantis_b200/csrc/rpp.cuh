@@ -30,6 +30,7 @@ __device__ inline void svd3(const M3& A, M3& U, double w[3], M3& V)
                     ga += a[k * 3 + p] * a[k * 3 + q];
                 }
                 if (fabs(ga) <= 1e-300 || fabs(ga) <= 2.220446049250313e-16 * sqrt(al * be)) continue;
+                if (al <= 1e-28 * be || be <= 1e-28 * al) continue; /* a numerically null column is already orthogonal */
                 changed = 1;
                 double zeta = (be - al) / (2.0 * ga);
                 double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));

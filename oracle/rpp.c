@@ -19,6 +19,10 @@
 
 #define MAXN MO_RPP_MAX_POINTS
 
+/* diagnostics: AbsKernel calls of the successive ObjPose runs of the last mo_rpp() */
+int mo_rpp_debug_iters[8];
+int mo_rpp_debug_n;
+
 typedef struct { double m[9]; } m3;
 typedef struct { double v[3]; } v3;
 
@@ -92,6 +96,7 @@ static void svd3(m3 A, m3* U, double w[3], m3* V)
                     ga += a[k * 3 + p] * a[k * 3 + q];
                 }
                 if (fabs(ga) <= 1e-300 || fabs(ga) <= 2.220446049250313e-16 * sqrt(al * be)) continue;
+                if (al <= 1e-28 * be || be <= 1e-28 * al) continue; /* a numerically null column is already orthogonal */
                 changed = 1;
                 double zeta = (be - al) / (2.0 * ga);
                 double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
@@ -329,6 +334,7 @@ static void obj_pose(const objpose_ctx* c, int has_init, m3 initR, m3* Rout, v3*
         *it += 1;
         if (*it > 100000) break; /* the reference has no cap; guard the oracle against NaN loops */
     }
+    if (mo_rpp_debug_n < 8) mo_rpp_debug_iters[mo_rpp_debug_n++] = *it;
     *Rout = Ri;
     *obj_err = sqrt(new_err / n);
     double ie = 0;
@@ -551,6 +557,7 @@ int mo_rpp(const double* model3xn, const double* iprts3xn, int n, double* R9, do
            double* obj_err, double* img_err)
 {
     if (n < 3 || n > MAXN) return 0;
+    mo_rpp_debug_n = 0;
     objpose_ctx c;
     objpose_setup(&c, model3xn, iprts3xn, n);
     m3 Rlu;

@@ -63,3 +63,20 @@ def test_quads_nested_and_thin_shapes(ctx):
     tr, _ = po.localize(img, K_for(160, 120), np.zeros(4))
     check_quads(fq, tr)
     assert tr.n_contours >= 6
+
+
+def test_device_renderer_matches_oracle(ctx):
+    """The CUDA ray-caster against the oracle's: identical up to boundary pixels where the two
+    libm's tan/atan differ in the last bit."""
+    import torch
+
+    K, D = K_for(640, 480), np.zeros(4)
+    ps = poses(4, seed=99)
+    buf = torch.empty((len(ps), 480, 640, 3), dtype=torch.uint8, device="cuda:0")
+    ctx.render_grid_device(ps, 640, 480, K, D, buf.data_ptr())
+    got = buf.cpu().numpy()
+    for i, (R, t) in enumerate(ps):
+        ref = po.render_grid(R, t, K, D, 640, 480)
+        diff = (got[i] != ref).any(axis=2).mean()
+        assert diff < 1e-4, diff
+        assert (ref > 200).any()
