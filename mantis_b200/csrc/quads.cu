@@ -6,31 +6,57 @@
 //   Quadrilateral ctor (centre, side, stretched test points)  :13-66
 //   removeDuplicateQuads                                     :115-171
 //
-// Suzuki-Abe border following is a sequential raster scan in OpenCV; here every border is found
-// and traced independently:
-//   1. candidates: a border can only start at a local top-left extreme -- an outer border at a
-//      foreground pixel with no foreground W/NW/N/NE neighbour, a hole border at a background
-//      pixel whose W and N neighbours are foreground (bit tests on whole words).
-//   2. one thread per candidate follows its border and gives up as soon as it meets a pixel that
-//      the raster scan would have reached earlier (or, for holes, the image frame); a candidate
-//      that closes its loop is exactly a border start of the sequential algorithm.
-//   3. starts are ranked in raster order (= OpenCV's discovery order); each border is traced
-//      again to emit its CHAIN_APPROX_SIMPLE points and to record which border owns each
-//      left edge it passes (needed for the hole -> component relation of RETR_CCOMP).
-//   4. approxPolyDP per border (OpenCV 4.13 variant: distance to the SEGMENT), CCOMP ordering
-//      (outer borders in reverse discovery order, each followed by its holes, reversed).
+// Suzuki-Abe border following is a sequential raster scan in OpenCV.  Here every border of every
+// frame of the batch is found and traced independently, in five flat launches:
+//   k_qcand   word-parallel candidate detection.  A border can only start at the raster-first pixel
+//             of its component: an outer border at the first pixel of a foreground run that has no
+//             foreground anywhere above it (8-connectivity: columns start-1 .. end+1 of the row
+//             above), a hole border at the first pixel of a background run whose left neighbour is
+//             foreground and that has no background above it (4-connectivity: columns start .. end).
+//   k_qprobe  one thread per candidate follows its border and gives up as soon as it meets a pixel
+//             that the raster scan would have reached earlier (or, for holes, the image frame); a
+//             candidate that closes its loop is exactly a border start of the sequential algorithm.
+//   k_qrank   per frame: starts ranked in raster order (= OpenCV's discovery order), point offsets,
+//             and a by-length order so that the warps of the next launch get similar borders.
+//   k_qtrace  one thread per border: second walk emitting the CHAIN_APPROX_SIMPLE vertices and
+//             recording which border owns each left edge it passes (hole -> component relation of
+//             RETR_CCOMP), then approxPolyDP (OpenCV 4.13 variant: distance to the SEGMENT).
+//   k_qfinish per frame: hole parents, CCOMP ordering (outer borders in reverse discovery order,
+//             each followed by its holes, reversed), Quadrilateral ctor, de-duplication, output.
+// A walk step is branch-light: the 3x3 neighbourhood comes from three word loads, the next
+// direction from a rotate + find-first-set on the 8-bit neighbour mask.
 #include "ctx.h"
 #include "pipeline.cuh"
 
 namespace {
 
-constexpr int QNT = 256;
 constexpr int MAXB = MANTIS_MAX_BORDERS;   // border starts per frame
-constexpr int MAXCAND = 4096;              // queued candidates (more are walked inline)
+constexpr int MAXCAND = 16384;             // candidates per frame
+constexpr int CNT = 256;
 
 struct BitImg {
     const uint32_t* bits;
     int W, H, WW;
+    // bits x-1, x, x+1 of row y (0 outside the image) in bits 0..2
+    __device__ __forceinline__ uint32_t get3(int x, int y) const
+    {
+        if ((unsigned)y >= (unsigned)H) return 0u;
+        const uint32_t* row = bits + (size_t)y * WW;
+        const int j = x >> 5, b = x & 31;
+        uint32_t w = __ldg(row + j), v;
+        if (b == 0) v = (w << 1) | (j > 0 ? (__ldg(row + j - 1) >> 31) : 0u);
+        else if (b == 31) v = (w >> 30) | ((j + 1 < WW ? (__ldg(row + j + 1) & 1u) : 0u) << 2);
+        else v = w >> (b - 1);
+        return v & 7u;
+    }
+    // 8-neighbour mask of (x, y): bit d set iff the pixel in direction d is foreground
+    // directions: 0 E, 1 NE, 2 N, 3 NW, 4 W, 5 SW, 6 S, 7 SE (image coordinates, y down)
+    __device__ __forceinline__ uint32_t nbr(int x, int y) const
+    {
+        uint32_t up = get3(x, y - 1), mid = get3(x, y), dn = get3(x, y + 1);
+        return ((mid >> 2) & 1u) | (((up >> 2) & 1u) << 1) | (((up >> 1) & 1u) << 2) | ((up & 1u) << 3) |
+               ((mid & 1u) << 4) | ((dn & 1u) << 5) | (((dn >> 1) & 1u) << 6) | (((dn >> 2) & 1u) << 7);
+    }
     __device__ __forceinline__ int at(int x, int y) const
     {
         if ((unsigned)x >= (unsigned)W || (unsigned)y >= (unsigned)H) return 0;
@@ -38,8 +64,8 @@ struct BitImg {
     }
 };
 
-__constant__ int c_dx[8] = {1, 1, 0, -1, -1, -1, 0, 1};
-__constant__ int c_dy[8] = {0, -1, -1, -1, 0, 1, 1, 1};
+__device__ __forceinline__ int dir_dx(int s) { return (int)((0x901Au >> (2 * s)) & 3u) - 1; }
+__device__ __forceinline__ int dir_dy(int s) { return (int)((0xA901u >> (2 * s)) & 3u) - 1; }
 
 // Border following (OpenCV's icvFetchContour on a 0/1 image with a zero frame).
 // Visitor:  bool step(x, y, zmask)  -- called for every border pixel with the set of directions
@@ -49,65 +75,69 @@ __constant__ int c_dy[8] = {0, -1, -1, -1, 0, 1, 1, 1};
 template <class V>
 __device__ bool follow_border(const BitImg& im, int x0, int y0, bool is_hole, V& vis)
 {
-    int s_end = is_hole ? 0 : 4, s = s_end;
-    int nz;
-    do {
-        s = (s - 1) & 7;
-        nz = im.at(x0 + c_dx[s], y0 + c_dy[s]);
-    } while (!nz && s != s_end);
-    if (s == s_end) {  // isolated pixel
+    const int s_end = is_hole ? 0 : 4;
+    uint32_t nb = im.nbr(x0, y0);
+    int s = -1;
+    for (int k = 1; k < 8; ++k) {  // clockwise from s_end - 1
+        int d = (s_end - k) & 7;
+        if ((nb >> d) & 1u) { s = d; break; }
+    }
+    if (s < 0) {  // isolated pixel
         if (!vis.step(x0, y0, 0xffu)) return false;
         vis.point(x0, y0);
         return true;
     }
-    const int x1 = x0 + c_dx[s], y1 = y0 + c_dy[s];
+    const int x1 = x0 + dir_dx(s), y1 = y0 + dir_dy(s);
     int x3 = x0, y3 = y0, prev_s = s ^ 4;
     for (;;) {
-        s_end = s;
-        unsigned zmask = 0;
-        int x4, y4;
-        for (;;) {
-            ++s;
-            x4 = x3 + c_dx[s & 7];
-            y4 = y3 + c_dy[s & 7];
-            if (im.at(x4, y4)) break;
-            zmask |= 1u << (s & 7);
-        }
-        s &= 7;
-        if (!vis.step(x3, y3, zmask)) return false;
+        // counter-clockwise from s + 1: first foreground neighbour
+        const int r0 = (s + 1) & 7;
+        const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
+        const int k = __ffs(rot) - 1;
+        uint32_t z = ((1u << k) - 1u) << r0;
+        z = (z | (z >> 8)) & 0xffu;
+        s = (r0 + k) & 7;
+        if (!vis.step(x3, y3, z)) return false;
         if (s != prev_s) {
             vis.point(x3, y3);
             prev_s = s;
         }
+        const int x4 = x3 + dir_dx(s), y4 = y3 + dir_dy(s);
         if (x4 == x0 && y4 == y0 && x3 == x1 && y3 == y1) break;
         x3 = x4;
         y3 = y4;
         s = (s + 4) & 7;
+        nb = im.nbr(x3, y3);
     }
     return true;
 }
 
 // detection visitor: outer borders
 struct OuterProbe {
-    int x0, y0, npts;
-    __device__ bool step(int x, int y, unsigned) { return !(y < y0 || (y == y0 && x < x0)); }
-    __device__ void point(int, int) { ++npts; }
+    int x0, y0, npts, steps;
+    __device__ __forceinline__ bool step(int x, int y, unsigned)
+    {
+        ++steps;
+        return !(y < y0 || (y == y0 && x < x0));
+    }
+    __device__ __forceinline__ void point(int, int) { ++npts; }
 };
 // detection visitor: hole borders; (hx, hy) is the hole's first background pixel
 struct HoleProbe {
-    int hx, hy, W, H, npts;
-    __device__ bool step(int x, int y, unsigned zmask)
+    int hx, hy, W, H, npts, steps;
+    __device__ __forceinline__ bool step(int x, int y, unsigned zmask)
     {
+        ++steps;
 #pragma unroll
         for (int d = 0; d < 8; d += 2) {
             if (!(zmask & (1u << d))) continue;
-            int bx = x + c_dx[d], by = y + c_dy[d];
+            int bx = x + dir_dx(d), by = y + dir_dy(d);
             if ((unsigned)bx >= (unsigned)W || (unsigned)by >= (unsigned)H) return false;  // touches the frame
             if (by < hy || (by == hy && bx < hx)) return false;
         }
         return true;
     }
-    __device__ void point(int, int) { ++npts; }
+    __device__ __forceinline__ void point(int, int) { ++npts; }
 };
 // extraction visitor
 struct Emit {
@@ -115,14 +145,13 @@ struct Emit {
     uint16_t* owner;
     int W, n;
     uint16_t id;
-    __device__ bool step(int x, int y, unsigned zmask)
+    __device__ __forceinline__ bool step(int x, int y, unsigned zmask)
     {
         if (zmask & (1u << 4)) owner[(size_t)y * W + x] = id;  // this border owns the left edge of (x, y)
         return true;
     }
-    __device__ void point(int x, int y) { out[n++] = make_short2((short)x, (short)y); }
+    __device__ __forceinline__ void point(int x, int y) { out[n++] = make_short2((short)x, (short)y); }
 };
-
 // cv::approxPolyDP for a closed int contour (see oracle/approx.c for the algorithm notes).
 __device__ int approx_poly_closed(const short2* src, int count, double eps, short2* dst, int2* stack)
 {
@@ -218,6 +247,389 @@ __device__ int approx_poly_closed(const short2* src, int count, double eps, shor
     return new_count;
 }
 
+
+struct QMeta {  // per frame, zeroed before every batch
+    int ncand, nstart, flags, nb;
+};
+
+struct QuadArgs {
+    const uint32_t* morph_bits;
+    int W, H, WW, n_frames;
+    QMeta* meta;          // [n]
+    uint32_t* cand;       // [n][MAXCAND]
+    uint32_t* ukey;       // [n][MAXB] unsorted starts: key, vertex count, walk length
+    int* unp;
+    int* usteps;
+    uint32_t* key;        // [n][MAXB] sorted by discovery order
+    int* np;
+    int* off;
+    short* bylen;         // [n][MAXB] border indices, longest walk first
+    short* an;            // [n][MAXB] approxPolyDP vertex count
+    short2* quad;         // [n][MAXB][4]
+    short2* pts;          // [n][MANTIS_MAX_PTS]
+    short2* dst;          // [n][MANTIS_MAX_PTS]
+    int2* stack;          // [n][MANTIS_MAX_PTS + 2 * MAXB]
+    uint16_t* owner;      // [n][W * H]
+    FrameQuads* out;
+    double eps, stretch, radius_mult;
+};
+
+__device__ __forceinline__ uint32_t bits_at(const uint32_t* p, int WW, int H, int y, int j)
+{
+    if (y < 0 || y >= H || j < 0 || j >= WW) return 0u;
+    return __ldg(p + (size_t)y * WW + j);
+}
+
+// length of the run of ones of `t` starting at bit 0 (0..32)
+__device__ __forceinline__ int ones_from0(uint32_t t)
+{
+    int f = __ffs(~t);
+    return f ? f - 1 : 32;
+}
+
+// ---- 1. candidates -------------------------------------------------------------------------
+__global__ void __launch_bounds__(CNT) k_qcand(QuadArgs a)
+{
+    const int W = a.W, H = a.H, WW = a.WW, frame = blockIdx.y;
+    const int i = blockIdx.x * CNT + threadIdx.x;
+    if (i >= H * WW) return;
+    const uint32_t* bits = a.morph_bits + (size_t)frame * H * WW;
+    const int y = i / WW, j = i - y * WW;
+    const uint32_t c = bits_at(bits, WW, H, y, j), cp = bits_at(bits, WW, H, y, j - 1);
+    const uint32_t left = (c << 1) | (cp >> 31);
+    const uint32_t valid = (j == WW - 1 && (W & 31)) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
+    uint32_t outer = c & ~left;                          // first pixels of foreground runs
+    uint32_t hole = (y > 0) ? (~c & left & valid) : 0u;  // first pixels of background runs right of foreground
+    if (!(outer | hole)) return;
+    QMeta* meta = a.meta + frame;
+
+    auto dilated_above = [&](int jj) {  // foreground of row y-1 at columns p-1, p, p+1, for the columns p of word jj
+        uint32_t u = bits_at(bits, WW, H, y - 1, jj);
+        return u | (u << 1) | (bits_at(bits, WW, H, y - 1, jj - 1) >> 31) | (u >> 1) | (bits_at(bits, WW, H, y - 1, jj + 1) << 31);
+    };
+    auto push = [&](uint32_t v) {
+        int k = atomicAdd(&meta->ncand, 1);
+        if (k < MAXCAND) a.cand[(size_t)frame * MAXCAND + k] = v;
+        else atomicOr(&meta->flags, FRAME_FLAG_BORDER_OVERFLOW);
+    };
+
+    while (outer) {
+        const int b = __ffs(outer) - 1;
+        outer &= outer - 1;
+        // follow the run to the right; reject as soon as foreground shows up above it
+        bool ok = true;
+        int jj = j, bb = b;
+        uint32_t w = c;
+        for (;;) {
+            int len = ones_from0(w >> bb);                    // run pixels inside this word: bb .. bb+len-1
+            uint32_t m = (len >= 32 ? 0xffffffffu : ((1u << len) - 1u)) << bb;
+            if (m & dilated_above(jj)) { ok = false; break; }
+            if (bb + len < 32 || jj + 1 >= WW) break;         // run ended inside the word / at the last word
+            ++jj; bb = 0;
+            w = bits_at(bits, WW, H, y, jj);
+            if (!(w & 1u)) break;
+        }
+        if (ok) push(((uint32_t)y << 15) | (uint32_t)(j * 32 + b));
+    }
+    while (hole) {
+        const int b = __ffs(hole) - 1;
+        hole &= hole - 1;
+        // follow the background run; reject on background above it or on reaching the right frame
+        bool ok = true;
+        int jj = j, bb = b;
+        uint32_t w = ~c;
+        for (;;) {
+            const uint32_t vj = (jj == WW - 1 && (W & 31)) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
+            int len = ones_from0((w & vj) >> bb);
+            uint32_t m = (len >= 32 ? 0xffffffffu : ((1u << len) - 1u)) << bb;
+            if (m & ~bits_at(bits, WW, H, y - 1, jj)) { ok = false; break; }
+            const int xe = jj * 32 + bb + len;                // first column after the run part
+            if (xe >= W) { ok = false; break; }               // background run reaches the frame
+            if (bb + len < 32) break;
+            ++jj; bb = 0;
+            w = ~bits_at(bits, WW, H, y, jj);
+            if (!(w & 1u)) break;
+        }
+        if (ok) push(0x80000000u | ((uint32_t)y << 15) | (uint32_t)(j * 32 + b));
+    }
+}
+
+// ---- 2. probe walks ------------------------------------------------------------------------
+__global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a)
+{
+    const int frame = blockIdx.y, i = blockIdx.x * CNT + threadIdx.x;
+    QMeta* meta = a.meta + frame;
+    if (i >= min(meta->ncand, MAXCAND)) return;
+    const int W = a.W, H = a.H;
+    BitImg im;
+    im.bits = a.morph_bits + (size_t)frame * H * a.WW;
+    im.W = W; im.H = H; im.WW = a.WW;
+    const uint32_t cand = a.cand[(size_t)frame * MAXCAND + i];
+    const bool is_hole = cand >> 31;
+    const int y = (cand >> 15) & 0xffff, x = cand & 0x7fff;
+    int np, steps;
+    bool ok;
+    if (!is_hole) {
+        OuterProbe v{x, y, 0, 0};
+        ok = follow_border(im, x, y, false, v);
+        np = v.npts; steps = v.steps;
+    } else {
+        HoleProbe v{x, y, W, H, 0, 0};
+        ok = follow_border(im, x - 1, y, true, v);
+        np = v.npts; steps = v.steps;
+    }
+    if (!ok) return;
+    int k = atomicAdd(&meta->nstart, 1);
+    if (k >= MAXB) { atomicOr(&meta->flags, FRAME_FLAG_BORDER_OVERFLOW); return; }
+    const size_t o = (size_t)frame * MAXB + k;
+    a.ukey[o] = ((uint32_t)(y * (W + 1) + x) << 1) | (is_hole ? 1u : 0u);
+    a.unp[o] = np;
+    a.usteps[o] = steps;
+}
+
+// ---- 3. discovery order, point offsets, by-length order ---------------------------------------
+__global__ void __launch_bounds__(CNT) k_qrank(QuadArgs a)
+{
+    __shared__ uint32_t s_ukey[MAXB];
+    __shared__ int s_ust[MAXB];
+    __shared__ int s_np[MAXB], s_st[MAXB];
+    const int frame = blockIdx.x, tid = threadIdx.x;
+    QMeta* meta = a.meta + frame;
+    const int nb = min(meta->nstart, MAXB);
+    const size_t base = (size_t)frame * MAXB;
+    for (int i = tid; i < nb; i += CNT) { s_ukey[i] = a.ukey[base + i]; s_ust[i] = a.usteps[base + i]; }
+    __syncthreads();
+    for (int i = tid; i < nb; i += CNT) {
+        const uint32_t k = s_ukey[i];
+        int r = 0;
+        for (int j = 0; j < nb; ++j) r += s_ukey[j] < k;
+        a.key[base + r] = k;
+        s_np[r] = a.unp[base + i];
+        s_st[r] = s_ust[i];
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int acc = 0;
+        for (int i = 0; i < nb; ++i) { a.off[base + i] = acc; acc += s_np[i]; }
+        if (acc > MANTIS_MAX_PTS) meta->flags |= FRAME_FLAG_POINT_OVERFLOW;
+        meta->nb = nb;
+    }
+    for (int i = tid; i < nb; i += CNT) {
+        a.np[base + i] = s_np[i];
+        const int st = s_st[i];
+        int r = 0;  // position by descending walk length (ties by index)
+        for (int j = 0; j < nb; ++j) r += (s_st[j] > st) || (s_st[j] == st && j < i);
+        a.bylen[base + r] = (short)i;
+    }
+}
+
+// ---- 4. extraction + approxPolyDP, one thread per border --------------------------------------
+constexpr int TNT = 64;
+__global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a)
+{
+    const int frame = blockIdx.y, slot = blockIdx.x * TNT + threadIdx.x;
+    const QMeta* meta = a.meta + frame;
+    if (meta->flags || slot >= meta->nb) return;
+    const int W = a.W, H = a.H;
+    const size_t base = (size_t)frame * MAXB;
+    const int b = a.bylen[base + slot];
+    BitImg im;
+    im.bits = a.morph_bits + (size_t)frame * H * a.WW;
+    im.W = W; im.H = H; im.WW = a.WW;
+    const uint32_t k = a.key[base + b];
+    const bool is_hole = k & 1u;
+    const int p = (int)(k >> 1), y = p / (W + 1), x = p - y * (W + 1);
+    const int off = a.off[base + b], np = a.np[base + b];
+    short2* pts = a.pts + (size_t)frame * MANTIS_MAX_PTS + off;
+    short2* dst = a.dst + (size_t)frame * MANTIS_MAX_PTS + off;
+    int2* stack = a.stack + (size_t)frame * (MANTIS_MAX_PTS + 2 * MAXB) + off + 2 * b;
+    Emit v{pts, a.owner + (size_t)frame * W * H, W, 0, (uint16_t)b};
+    follow_border(im, is_hole ? x - 1 : x, y, is_hole, v);
+    const int n4 = approx_poly_closed(pts, np, a.eps, dst, stack);
+    a.an[base + b] = (short)min(n4, 32767);
+    if (n4 == 4)
+        for (int q = 0; q < 4; ++q) a.quad[(base + b) * 4 + q] = dst[q];
+}
+
+// ---- 5. hole parents, CCOMP order, quads, de-duplication, output (per frame) --------------------
+constexpr int FNT = 128;
+__global__ void __launch_bounds__(FNT) k_qfinish(QuadArgs a)
+{
+    __shared__ uint32_t s_key[MAXB];
+    __shared__ short s_parent[MAXB];
+    __shared__ short s_pos2b[MAXB];
+    __shared__ short s_an[MAXB];
+    __shared__ float s_cx[MANTIS_MAX_QUADS], s_cy[MANTIS_MAX_QUADS];
+    __shared__ short s_qb[MANTIS_MAX_QUADS];
+    __shared__ unsigned char s_neighbor[MANTIS_MAX_QUADS];
+    __shared__ int s_nraw, s_qflag;
+
+    const int frame = blockIdx.x, tid = threadIdx.x;
+    const int W = a.W, H = a.H;
+    const QMeta* meta = a.meta + frame;
+    FrameQuads* out = a.out + frame;
+    const int flags = meta->flags;
+    const int nb = flags ? min(meta->nstart, MAXB) : meta->nb;
+    if (flags) {
+        if (tid == 0) { out->n_contours = nb; out->flags = flags; out->n_quads_raw = 0; out->n_quads = 0; }
+        return;
+    }
+    const size_t base = (size_t)frame * MAXB;
+    BitImg im;
+    im.bits = a.morph_bits + (size_t)frame * H * a.WW;
+    im.W = W; im.H = H; im.WW = a.WW;
+    const uint16_t* owner = a.owner + (size_t)frame * W * H;
+    for (int b = tid; b < nb; b += FNT) { s_key[b] = a.key[base + b]; s_an[b] = a.an[base + b]; }
+    __syncthreads();
+    // hole -> outer border of its component
+    for (int b = tid; b < nb; b += FNT) {
+        int cur = b;
+        while (s_key[cur] & 1u) {  // climb: left end of the foreground run left of the hole start
+            int p = (int)(s_key[cur] >> 1), y = p / (W + 1), x = p - y * (W + 1);
+            int xl = x - 1;
+            while (im.at(xl - 1, y)) --xl;
+            cur = owner[(size_t)y * W + xl];
+        }
+        s_parent[b] = (short)cur;
+    }
+    __syncthreads();
+    // CCOMP output order: outers by descending rank, each followed by its holes, descending
+    for (int b = tid; b < nb; b += FNT) {
+        bool hole_b = s_key[b] & 1u;
+        int top_b = s_parent[b];
+        int pos = 0;
+        for (int o = 0; o < nb; ++o) {
+            if (o == b) continue;
+            bool hole_o = s_key[o] & 1u;
+            int top_o = s_parent[o];
+            bool before;
+            if (top_o != top_b) before = top_o > top_b;
+            else if (hole_o != hole_b) before = !hole_o;
+            else before = o > b;
+            pos += before;
+        }
+        s_pos2b[pos] = (short)b;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int nraw = 0, qf = 0;
+        for (int p = 0; p < nb; ++p) {
+            int b = s_pos2b[p];
+            if (s_an[b] != 4) continue;
+            if (nraw >= MANTIS_MAX_QUADS) { qf = FRAME_FLAG_QUAD_OVERFLOW; break; }
+            s_qb[nraw++] = (short)b;
+        }
+        s_nraw = nraw;
+        s_qflag = qf;
+    }
+    __syncthreads();
+    const int nraw = s_nraw;
+    const short2* quad = a.quad + base * 4;
+    for (int e = tid; e < nraw; e += FNT) {
+        const short2* q = quad + 4 * s_qb[e];
+        float xs = 0.f, ys = 0.f;
+        for (int k = 0; k < 4; ++k) { xs += (float)q[k].x; ys += (float)q[k].y; }
+        s_cx[e] = xs / 4.f;
+        s_cy[e] = ys / 4.f;
+        s_neighbor[e] = 0;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        // removeDuplicateQuads: exact radius search, 4 results, unfilled slots alias quad 0.
+        // Sequential over quads as in the reference (a quad marked by an earlier one is skipped).
+        for (int e = 0; e < nraw; ++e) {
+            if (s_neighbor[e]) continue;
+            const short2* q = quad + 4 * s_qb[e];
+            int ddx = q[0].x - q[1].x, ddy = q[0].y - q[1].y;
+            double side = sqrt((double)(ddx * ddx + ddy * ddy));
+            float radius = (float)(a.radius_mult * side);
+            int idx[4] = {0, 0, 0, 0};
+            float dd[4];
+            int found = 0;
+            for (int j = 0; j < nraw; ++j) {
+                float fx = s_cx[e] - s_cx[j], fy = s_cy[e] - s_cy[j];
+                float d = __fadd_rn(__fmul_rn(fx, fx), __fmul_rn(fy, fy));
+                if (!(d <= radius)) continue;
+                int pos = found < 4 ? found : 4;
+                while (pos > 0 && dd[pos - 1] > d) --pos;
+                if (pos >= 4) continue;
+                int last = found < 4 ? found : 3;
+                for (int k = last; k > pos; --k) { dd[k] = dd[k - 1]; idx[k] = idx[k - 1]; }
+                dd[pos] = d;
+                idx[pos] = j;
+                if (found < 4) ++found;
+            }
+            for (int k = 1; k < 4; ++k) s_neighbor[idx[k]] = 1;
+        }
+        int nq = 0;
+        for (int e = 0; e < nraw; ++e) {
+            short slot = -1;
+            if (!s_neighbor[e]) slot = (short)nq++;
+            s_pos2b[e] = slot;  // reuse: raw quad -> output slot
+        }
+        out->n_contours = nb;
+        out->flags = s_qflag;
+        out->n_quads_raw = nraw;
+        out->n_quads = nq;
+    }
+    __syncthreads();
+    for (int e = tid; e < nraw; e += FNT) {
+        const int nq = s_pos2b[e];
+        if (nq < 0) continue;
+        const short2* q = quad + 4 * s_qb[e];
+        for (int k = 0; k < 4; ++k) {
+            int px = q[k].x, py = q[k].y;
+            out->corners[nq][2 * k] = px;
+            out->corners[nq][2 * k + 1] = py;
+            float ex = (float)px - s_cx[e], ey = (float)py - s_cy[e];
+            float mx = (float)((double)ex * a.stretch), my = (float)((double)ey * a.stretch);
+            out->test_px[nq][2 * k] = (double)__fadd_rn(mx, s_cx[e]);
+            out->test_px[nq][2 * k + 1] = (double)__fadd_rn(my, s_cy[e]);
+        }
+    }
+}
+
 }  // namespace
 
-#include "quads_kernel.inl"
+int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int h, FrameQuads* d_out)
+{
+    int rc;
+    const size_t nB = (size_t)n * MAXB;
+    // one arena: meta | cand | ukey unp usteps key np off | bylen an | quad
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
+    const size_t o_meta = take((size_t)n * sizeof(QMeta)), o_cand = take((size_t)n * MAXCAND * 4), o_ukey = take(nB * 4),
+                 o_unp = take(nB * 4), o_ust = take(nB * 4), o_key = take(nB * 4), o_np = take(nB * 4), o_off = take(nB * 4),
+                 o_bylen = take(nB * 2), o_an = take(nB * 2), o_quad = take(nB * 4 * sizeof(short2));
+    if ((rc = ctx_reserve(c, c->q_stack, o)) ||
+        (rc = ctx_reserve(c, c->q_pts, (size_t)n * MANTIS_MAX_PTS * sizeof(short2) * 2)) ||
+        (rc = ctx_reserve(c, c->q_dst, (size_t)n * (MANTIS_MAX_PTS + 2 * MAXB) * sizeof(int2))) ||
+        (rc = ctx_reserve(c, c->q_owner, (size_t)n * w * h * sizeof(uint16_t))))
+        return rc;
+    char* ar = (char*)c->q_stack.p;
+    QuadArgs a;
+    a.morph_bits = d_morph_bits;
+    a.W = w; a.H = h; a.WW = words_per_row(w); a.n_frames = n;
+    a.meta = (QMeta*)(ar + o_meta); a.cand = (uint32_t*)(ar + o_cand); a.ukey = (uint32_t*)(ar + o_ukey);
+    a.unp = (int*)(ar + o_unp); a.usteps = (int*)(ar + o_ust); a.key = (uint32_t*)(ar + o_key);
+    a.np = (int*)(ar + o_np); a.off = (int*)(ar + o_off); a.bylen = (short*)(ar + o_bylen);
+    a.an = (short*)(ar + o_an); a.quad = (short2*)(ar + o_quad);
+    a.pts = (short2*)c->q_pts.p;
+    a.dst = a.pts + (size_t)n * MANTIS_MAX_PTS;
+    a.stack = (int2*)c->q_dst.p;
+    a.owner = (uint16_t*)c->q_owner.p;
+    a.out = d_out;
+    a.eps = (double)c->cfg.polygon_epsilon;
+    a.stretch = c->cfg.quad_stretch_factor;
+    a.radius_mult = c->cfg.search_radius_multiplier;
+    MCHECK(c, cudaMemsetAsync(a.meta, 0, (size_t)n * sizeof(QMeta), c->stream));
+    const int words = h * a.WW;
+    k_qcand<<<dim3((words + CNT - 1) / CNT, n), CNT, 0, c->stream>>>(a);
+    k_qprobe<<<dim3(MAXCAND / CNT, n), CNT, 0, c->stream>>>(a);
+    k_qrank<<<n, CNT, 0, c->stream>>>(a);
+    k_qtrace<<<dim3(MAXB / TNT, n), TNT, 0, c->stream>>>(a);
+    k_qfinish<<<n, FNT, 0, c->stream>>>(a);
+    c->launches += 5;
+    MCHECK(c, cudaGetLastError());
+    return MANTIS_OK;
+}
