@@ -4,87 +4,223 @@
 //   generateHypotheses / generateCentralHypotheses   HypothesisGeneration.h:23-109
 //   PoseClusterer::clusterByAngle / BFcluster / keepLargestCluster / convert2Hypotheses
 //                                          PoseClusterer.cpp:33-116, PoseClusterer.h:59-115
-// One thread per quad runs RPP (rpp.cuh) for up to two corner orderings; passing quads emit four
+// RPP (rpp.cuh, rpp_fast.cuh) runs as a queue of independent ObjPose runs over all quads of the
+// batch (k_pose_run), for up to two corner orderings; passing quads emit four
 // yaw-rotated hypotheses in quad order.  The greedy Euler-space clustering is sequential over
 // seeds (as in the reference) and parallel over members.
 #include "ctx.h"
-#include "rpp.cuh"
+#include "rpp_fast.cuh"
 
 namespace {
 
 constexpr int PNT = 128;
 
+struct RunOut {   // result of one ObjPose run
+    double R[9], t[3], obj_err, img_err;
+};
+
+struct PoseCounters {   // zeroed before every batch
+    int n_t1[2];      // (quad, ordering) tasks of round 0 / 1
+    int n_t2[2];      // second-pose refinement runs of round 0 / 1
+    int fetch1[2], fetch2[2];
+};
+
 struct PoseArgs {
     const FrameQuads* quads;
     const pm::Camera* cams;  // per frame
+    int n_frames;
     Hyp* quad_hyp;           // [n][MANTIS_MAX_QUADS] RPP result of each passing quad
     Hyp* hyps;               // [n][MANTIS_MAX_HYPS]
     short* sel;              // [n][MANTIS_MAX_HYPS] members of the kept cluster
     FramePose* info;         // [n]
+    // workspace of the solve (cap = n * MANTIS_MAX_QUADS quads; an entry is quad * 2 + ordering)
+    PoseCounters* cnt;
+    double* rays;            // [cap][8] undistorted test points
+    int* list1;              // [2][cap] entries of round 0 / 1
+    int* list2;              // [2][cap * 4] entry * 4 + candidate
+    RunOut* run1;            // [cap * 2]
+    int* ncand;              // [cap * 2]
+    double* candR;           // [cap * 2 * 4][9]
+    RunOut* run2;            // [cap * 2 * 4]
+    int cap;
     double half_spacing, max_quad_error, cluster_radius;
     Tf rotz;                 // tf::Transform(tf::Quaternion(0, 0, 1/sqrt2, 1/sqrt2))
 };
 
-// Exclusive prefix sum of the per-frame quad counts: item i of the flattened work list belongs to
-// the frame f with offs[f] <= i < offs[f+1].
-__global__ void k_pose_index(const FrameQuads* quads, int n, int* offs)
+// gridSquarePossibilities, Mantis3Params.h:102-123
+__device__ __forceinline__ void model_xy(double s, int ordering, double* m)
 {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        int acc = 0;
-        for (int f = 0; f < n; ++f) { offs[f] = acc; acc += quads[f].n_quads; }
-        offs[n] = acc;
+    const double sx[2][4] = {{1, -1, -1, 1}, {1, -1, -1, 1}}, sy[2][4] = {{1, 1, -1, -1}, {-1, -1, 1, 1}};
+    for (int k = 0; k < 4; ++k) { m[2 * k] = sx[ordering][k] * s; m[2 * k + 1] = sy[ordering][k] * s; }
+}
+
+// ---- 1. undistort the test points, queue every quad with ordering 0 ---------------------------
+__global__ void __launch_bounds__(PNT) k_pose_prep(PoseArgs a)
+{
+    __shared__ int s_base;
+    const int frame = blockIdx.x, tid = threadIdx.x;
+    const FrameQuads* fq = a.quads + frame;
+    const int nq = fq->flags ? 0 : fq->n_quads;
+    if (tid == 0) s_base = nq ? atomicAdd(&a.cnt->n_t1[0], nq) : 0;
+    __syncthreads();
+    const pm::Camera cam = a.cams[frame];
+    for (int q = tid; q < nq; q += PNT) {
+        const int id = frame * MANTIS_MAX_QUADS + q;
+        for (int k = 0; k < 4; ++k)
+            pm::fisheye_undistort(cam, fq->test_px[q][2 * k], fq->test_px[q][2 * k + 1], a.rays[(size_t)id * 8 + 2 * k],
+                                  a.rays[(size_t)id * 8 + 2 * k + 1]);
+        a.list1[s_base + q] = id * 2;
     }
 }
 
-// One thread per (frame, quad): undistort the test points, RPP for up to two corner orderings
-// (generateCentralHypotheses, HypothesisGeneration.h:57-89).  Work items are flattened across the
-// frames of the batch so that warps are fully populated.
-__global__ void __launch_bounds__(PNT) k_pose_solve(PoseArgs a, const int* offs, int n_frames)
+// ---- 2. ObjPose runs, many per warp -------------------------------------------------------------
+// A lane owns one run at a time and advances it by one AbsKernel step per loop trip; finished
+// lanes pick up the next queued run every few trips, so lanes with short runs do not idle behind
+// long ones (runs take 2 .. several hundred steps).
+constexpr int RNT = 128;
+template <bool HAS_INIT>
+__global__ void __launch_bounds__(RNT) k_pose_run(PoseArgs a, int round)
 {
-    const int item = blockIdx.x * PNT + threadIdx.x;
-    if (item >= offs[n_frames]) return;
-    int lo = 0, hi = n_frames;  // last f with offs[f] <= item
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (offs[mid] <= item) lo = mid; else hi = mid;
+    __shared__ double s_ctx[rppf::CTX_WORDS][RNT];
+    const double TOL = 1e-5, EPSILON = 1e-8;
+    const int lane = threadIdx.x & 31;
+    double* ctx = &s_ctx[0][threadIdx.x];
+    const int* list = HAS_INIT ? a.list2 + (size_t)round * a.cap * 4 : a.list1 + (size_t)round * a.cap;
+    const int ntask = HAS_INIT ? a.cnt->n_t2[round] : a.cnt->n_t1[round];
+    int* fetch = HAS_INIT ? &a.cnt->fetch2[round] : &a.cnt->fetch1[round];
+    RunOut* out = HAS_INIT ? a.run2 : a.run1;
+    rppf::Lane L;
+    double old_err = 0, new_err = 0;
+    int task = -1, pending = 0, it = 0;
+    bool exhausted = false;
+    for (int trip = 0;; ++trip) {
+        if ((trip & 3) == 0) {
+            const bool want = task < 0 && !exhausted;
+            const unsigned need = __ballot_sync(0xffffffffu, want);
+            if (need) {
+                const int leader = __ffs(need) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(fetch, __popc(need));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (want) {
+                    const int my = base + __popc(need & ((1u << lane) - 1u));
+                    if (my < ntask) {
+                        task = list[my];
+                        const int entry = HAS_INIT ? (task >> 2) : task;
+                        double m[8];
+                        model_xy(a.half_spacing, entry & 1, m);
+                        rppf::setup(ctx, RNT, a.rays + (size_t)(entry >> 1) * 8, m);
+                        it = 0;
+                        if (HAS_INIT) {
+                            old_err = rppf::init_from_R(ctx, RNT, a.candR + (size_t)task * 9, L);
+                            pending = 1;
+                        } else {
+                            for (int i = 0; i < 4; ++i) {
+                                L.Q[i][0] = a.rays[(size_t)(entry >> 1) * 8 + 2 * i];
+                                L.Q[i][1] = a.rays[(size_t)(entry >> 1) * 8 + 2 * i + 1];
+                                L.Q[i][2] = 1.0;
+                            }
+                            pending = 2;
+                        }
+                    } else {
+                        exhausted = true;
+                    }
+                }
+            }
+            if (__ballot_sync(0xffffffffu, task >= 0) == 0) break;
+        }
+        if (task >= 0) {
+            const double e = rppf::abs_kernel(ctx, RNT, L);
+            bool stop = false;
+            if (pending == 2) {
+                old_err = e;
+                pending = 1;
+            } else {
+                if (pending == 0) old_err = new_err;
+                new_err = e;
+                pending = 0;
+                stop = !(fabs((old_err - new_err) / old_err) > TOL && new_err > EPSILON) || ++it > 100000;
+            }
+            if (stop) {
+                RunOut o;
+                rppf::finalize(ctx, RNT, L, new_err, o.R, o.t, o.obj_err, o.img_err);
+                out[task] = o;
+                task = -1;
+            }
+        }
     }
-    const int frame = lo, q = item - offs[lo];
-    const FrameQuads* fq = a.quads + frame;
-    const pm::Camera cam = a.cams[frame];
-    FramePose* info = a.info + frame;
+}
 
-    pm::V3 ray[4];
-    for (int k = 0; k < 4; ++k) {
-        pm::fisheye_undistort(cam, fq->test_px[q][2 * k], fq->test_px[q][2 * k + 1], ray[k].v[0], ray[k].v[1]);
-        ray[k].v[2] = 1.0;
+// ---- 3. second-pose candidates (RPP::Get2ndPose_Exact), one thread per queued quad --------------
+__global__ void __launch_bounds__(PNT) k_pose_second(PoseArgs a, int round)
+{
+    const int ntask = a.cnt->n_t1[round];
+    const int* list = a.list1 + (size_t)round * a.cap;
+    for (int i = blockIdx.x * PNT + threadIdx.x; i < ntask; i += gridDim.x * PNT) {
+        const int entry = list[i];
+        double m[8];
+        model_xy(a.half_spacing, entry & 1, m);
+        pm::V3 model[4], ray[4];
+        for (int k = 0; k < 4; ++k) {
+            model[k].v[0] = m[2 * k]; model[k].v[1] = m[2 * k + 1]; model[k].v[2] = 0;
+            ray[k].v[0] = a.rays[(size_t)(entry >> 1) * 8 + 2 * k];
+            ray[k].v[1] = a.rays[(size_t)(entry >> 1) * 8 + 2 * k + 1];
+            ray[k].v[2] = 1.0;
+        }
+        pm::M3 R, solR[4];
+        pm::V3 solT[4];
+        for (int k = 0; k < 9; ++k) R.m[k] = a.run1[entry].R[k];
+        const int ns = rpp::second_poses<4>(model, ray, R, solR, solT);
+        a.ncand[entry] = ns;
+        if (ns <= 0) continue;
+        const int base = atomicAdd(&a.cnt->n_t2[round], ns);
+        int* list2 = a.list2 + (size_t)round * a.cap * 4;
+        for (int c = 0; c < ns; ++c) {
+            for (int k = 0; k < 9; ++k) a.candR[((size_t)entry * 4 + c) * 9 + k] = solR[c].m[k];
+            list2[base + c] = entry * 4 + c;
+        }
     }
-    const double s = a.half_spacing;
-    // gridSquarePossibilities, Mantis3Params.h:102-123
-    const double poss[2][4][2] = {{{s, s}, {-s, s}, {-s, -s}, {s, -s}}, {{s, -s}, {-s, -s}, {-s, s}, {s, s}}};
-    double error = 1.7976931348623157e308;
-    bool failed = false;
-    Hyp h0;
-    for (int e = 0; e < 2; ++e) {
-        pm::V3 model[4];
-        for (int k = 0; k < 4; ++k) { model[k].v[0] = poss[e][k][0]; model[k].v[1] = poss[e][k][1]; model[k].v[2] = 0; }
-        pm::M3 R;
-        pm::V3 t;
-        double oe, ie;
-        if (!rpp::solve<4>(model, ray, R, t, oe, ie)) { failed = true; break; }
-        error = ie;
+}
+
+// ---- 4. best candidate -> hypothesis; wrong-side solutions queue the other corner ordering -------
+__global__ void __launch_bounds__(PNT) k_pose_select(PoseArgs a, int round)
+{
+    const int ntask = a.cnt->n_t1[round];
+    const int* list = a.list1 + (size_t)round * a.cap;
+    for (int i = blockIdx.x * PNT + threadIdx.x; i < ntask; i += gridDim.x * PNT) {
+        const int entry = list[i], id = entry >> 1;
+        const int frame = id / MANTIS_MAX_QUADS, q = id - frame * MANTIS_MAX_QUADS;
+        FramePose* info = a.info + frame;
+        const int ns = a.ncand[entry];
+        int best = -1;
+        double lowest = 1e6;
+        for (int c = 0; c < ns; ++c) {
+            const double oe = a.run2[(size_t)entry * 4 + c].obj_err;
+            if (oe < lowest) { lowest = oe; best = c; }
+        }
+        if (best < 0) {  // RPP::Rpp returned false: no second ordering is tried (HypothesisGeneration.h:62-66)
+            info->quad_img_err[q] = 1.7976931348623157e308;
+            info->quad_pass[q] = 0;
+            continue;
+        }
+        const RunOut& r = a.run2[(size_t)entry * 4 + best];
         Tf c2w;
-        for (int k = 0; k < 9; ++k) c2w.R[k] = R.m[k];
-        for (int k = 0; k < 3; ++k) c2w.t[k] = t.v[k];
+        for (int k = 0; k < 9; ++k) c2w.R[k] = r.R[k];
+        for (int k = 0; k < 3; ++k) c2w.t[k] = r.t[k];
+        Hyp h0;
         pm::hyp_set_c2w(h0, c2w);
-        if (h0.w2c.t[2] >= 0) break;
-    }
-    if (failed) error = 1.7976931348623157e308;
-    const bool pass = !failed && !(error > a.max_quad_error);
-    info->quad_img_err[q] = error;
-    info->quad_pass[q] = pass;
-    if (pass) {
-        h0.error = 0;
-        a.quad_hyp[(size_t)frame * MANTIS_MAX_QUADS + q] = h0;
+        if (round == 0 && !(h0.w2c.t[2] >= 0)) {
+            a.list1[(size_t)a.cap + atomicAdd(&a.cnt->n_t1[1], 1)] = id * 2 + 1;
+            continue;
+        }
+        const double error = r.img_err;
+        const bool pass = !(error > a.max_quad_error);
+        info->quad_img_err[q] = error;
+        info->quad_pass[q] = pass;
+        if (pass) {
+            h0.error = 0;
+            a.quad_hyp[(size_t)id] = h0;
+        }
     }
 }
 
@@ -208,24 +344,36 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
                 FramePose* d_info)
 {
     PoseArgs a;
-    a.quads = d_quads; a.cams = d_cams; a.hyps = d_hyps; a.sel = d_sel; a.info = d_info;
+    a.quads = d_quads; a.cams = d_cams; a.n_frames = n; a.hyps = d_hyps; a.sel = d_sel; a.info = d_info;
     a.half_spacing = c->cfg.grid_spacing / 2;
     a.max_quad_error = c->cfg.max_quad_error;
     a.cluster_radius = c->cfg.max_angle_difference;
     a.rotz = c->rotz;
+    const size_t cap = (size_t)n * MANTIS_MAX_QUADS;
+    a.cap = (int)cap;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
+    const size_t o_cnt = take(sizeof(PoseCounters)), o_rays = take(cap * 8 * sizeof(double)), o_l1 = take(cap * 2 * sizeof(int)),
+                 o_l2 = take(cap * 8 * sizeof(int)), o_run1 = take(cap * 2 * sizeof(RunOut)), o_nc = take(cap * 2 * sizeof(int)),
+                 o_cr = take(cap * 8 * 9 * sizeof(double)), o_run2 = take(cap * 8 * sizeof(RunOut));
     int rc;
-    if ((rc = ctx_reserve(c, c->quad_hyp, (size_t)n * MANTIS_MAX_QUADS * sizeof(Hyp))) ||
-        (rc = ctx_reserve(c, c->pose_offs, (size_t)(n + 1) * sizeof(int))))
-        return rc;
+    if ((rc = ctx_reserve(c, c->quad_hyp, cap * sizeof(Hyp))) || (rc = ctx_reserve(c, c->pose_offs, o))) return rc;
+    char* ws = (char*)c->pose_offs.p;
     a.quad_hyp = (Hyp*)c->quad_hyp.p;
-    int* offs = (int*)c->pose_offs.p;
-    k_pose_index<<<1, 32, 0, c->stream>>>(d_quads, n, offs);
-    // the item count is only known on the device: launch for the capacity and let spare threads exit
-    // (upper bound tightened with the previous stage's counts would need a sync)
-    const int max_items = n * MANTIS_MAX_QUADS;
-    k_pose_solve<<<(max_items + PNT - 1) / PNT, PNT, 0, c->stream>>>(a, offs, n);
+    a.cnt = (PoseCounters*)(ws + o_cnt); a.rays = (double*)(ws + o_rays); a.list1 = (int*)(ws + o_l1);
+    a.list2 = (int*)(ws + o_l2); a.run1 = (RunOut*)(ws + o_run1); a.ncand = (int*)(ws + o_nc);
+    a.candR = (double*)(ws + o_cr); a.run2 = (RunOut*)(ws + o_run2);
+    MCHECK(c, cudaMemsetAsync(a.cnt, 0, sizeof(PoseCounters), c->stream));
+    k_pose_prep<<<n, PNT, 0, c->stream>>>(a);
+    const int run_blocks = c->sm_count * 4, flat_blocks = c->sm_count * 4;
+    for (int round = 0; round < 2; ++round) {
+        k_pose_run<false><<<run_blocks, RNT, 0, c->stream>>>(a, round);
+        k_pose_second<<<flat_blocks, PNT, 0, c->stream>>>(a, round);
+        k_pose_run<true><<<run_blocks, RNT, 0, c->stream>>>(a, round);
+        k_pose_select<<<flat_blocks, PNT, 0, c->stream>>>(a, round);
+    }
     k_pose_cluster<<<n, PNT, 0, c->stream>>>(a);
-    c->launches += 3;
+    c->launches += 10;
     MCHECK(c, cudaGetLastError());
     return MANTIS_OK;
 }

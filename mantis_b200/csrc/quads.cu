@@ -43,9 +43,9 @@ struct BitImg {
         if ((unsigned)y >= (unsigned)H) return 0u;
         const uint32_t* row = bits + (size_t)y * WW;
         const int j = x >> 5, b = x & 31;
-        uint32_t w = __ldg(row + j), v;
-        if (b == 0) v = (w << 1) | (j > 0 ? (__ldg(row + j - 1) >> 31) : 0u);
-        else if (b == 31) v = (w >> 30) | ((j + 1 < WW ? (__ldg(row + j + 1) & 1u) : 0u) << 2);
+        uint32_t w = row[j], v;
+        if (b == 0) v = (w << 1) | (j > 0 ? (row[j - 1] >> 31) : 0u);
+        else if (b == 31) v = (w >> 30) | ((j + 1 < WW ? (row[j + 1] & 1u) : 0u) << 2);
         else v = w >> (b - 1);
         return v & 7u;
     }
@@ -60,7 +60,7 @@ struct BitImg {
     __device__ __forceinline__ int at(int x, int y) const
     {
         if ((unsigned)x >= (unsigned)W || (unsigned)y >= (unsigned)H) return 0;
-        return (__ldg(bits + (size_t)y * WW + (x >> 5)) >> (x & 31)) & 1;
+        return (bits[(size_t)y * WW + (x >> 5)] >> (x & 31)) & 1;
     }
 };
 
@@ -152,6 +152,39 @@ struct Emit {
     }
     __device__ __forceinline__ void point(int x, int y) { out[n++] = make_short2((short)x, (short)y); }
 };
+// approxPolyDP's final pass: drops (almost) collinear vertices of dst[0..count), in place.
+__device__ int approx_cleanup(short2* dst, int count, double eps)
+{
+    int new_count = count;
+    short2 start_pt, end_pt, pt;
+    int pos = count - 1;
+    start_pt = dst[pos];
+    if (++pos >= count) pos = 0;
+    int wpos = pos;
+    pt = dst[pos];
+    if (++pos >= count) pos = 0;
+    for (int i = 0; i < count && new_count > 2; ++i) {
+        end_pt = dst[pos];
+        if (++pos >= count) pos = 0;
+        double dx = end_pt.x - start_pt.x, dy = end_pt.y - start_pt.y;
+        double dist = fabs((pt.x - start_pt.x) * dy - (pt.y - start_pt.y) * dx);
+        double sip = (double)(pt.x - start_pt.x) * (end_pt.x - pt.x) + (double)(pt.y - start_pt.y) * (end_pt.y - pt.y);
+        if (dist * dist <= 0.5 * eps * (dx * dx + dy * dy) && dx != 0 && dy != 0 && sip >= 0) {
+            new_count--;
+            dst[wpos] = start_pt = end_pt;
+            if (++wpos >= count) wpos = 0;
+            pt = dst[pos];
+            if (++pos >= count) pos = 0;
+            i++;
+            continue;
+        }
+        dst[wpos] = start_pt = pt;
+        if (++wpos >= count) wpos = 0;
+        pt = end_pt;
+    }
+    return new_count;
+}
+
 // cv::approxPolyDP for a closed int contour (see oracle/approx.c for the algorithm notes).
 __device__ int approx_poly_closed(const short2* src, int count, double eps, short2* dst, int2* stack)
 {
@@ -217,40 +250,110 @@ __device__ int approx_poly_closed(const short2* src, int count, double eps, shor
             stack[top++] = slice;
         }
     }
-    // clean-up of (almost) collinear vertices
-    count = new_count;
-    pos = count - 1;
-    start_pt = dst[pos];
-    if (++pos >= count) pos = 0;
-    int wpos = pos;
-    pt = dst[pos];
-    if (++pos >= count) pos = 0;
-    for (int i = 0; i < count && new_count > 2; ++i) {
-        end_pt = dst[pos];
-        if (++pos >= count) pos = 0;
-        double dx = end_pt.x - start_pt.x, dy = end_pt.y - start_pt.y;
-        double dist = fabs((pt.x - start_pt.x) * dy - (pt.y - start_pt.y) * dx);
-        double sip = (double)(pt.x - start_pt.x) * (end_pt.x - pt.x) + (double)(pt.y - start_pt.y) * (end_pt.y - pt.y);
-        if (dist * dist <= 0.5 * eps * (dx * dx + dy * dy) && dx != 0 && dy != 0 && sip >= 0) {
-            new_count--;
-            dst[wpos] = start_pt = end_pt;
-            if (++wpos >= count) wpos = 0;
-            pt = dst[pos];
-            if (++pos >= count) pos = 0;
-            i++;
-            continue;
-        }
-        dst[wpos] = start_pt = pt;
-        if (++wpos >= count) wpos = 0;
-        pt = end_pt;
-    }
-    return new_count;
+    return approx_cleanup(dst, new_count, eps);
 }
 
 
+// (dist, order) arg-max over the warp: larger dist wins, ties go to the smaller order (= the
+// element a sequential `dist > max_dist` scan would have kept).
+__device__ __forceinline__ void warp_argmax_first(double& d, int& ord)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double d2 = __shfl_xor_sync(0xffffffffu, d, o);
+        int o2 = __shfl_xor_sync(0xffffffffu, ord, o);
+        if (d2 > d || (d2 == d && o2 < ord)) { d = d2; ord = o2; }
+    }
+}
+
+// approx_poly_closed with the point scans spread over a warp (all 32 lanes call it with the same
+// arguments; the result is identical to the sequential version).  Used for long contours.
+__device__ int approx_poly_closed_warp(const short2* src, int count, double eps, short2* dst, int2* stack)
+{
+    if (count == 0) return 0;
+    const int lane = threadIdx.x & 31;
+    int new_count = 0, top = 0, pos = 0;
+    int2 slice = make_int2(0, 0), right = make_int2(0, 0);
+    short2 start_pt = make_short2(0, 0), end_pt;
+    bool le_eps = false;
+    eps *= eps;
+    for (int i = 0; i < 3; ++i) {
+        pos = (pos + right.x) % count;     // index of the start point; the scan returns to it
+        start_pt = src[pos];
+        double best = 0;
+        int bj = 0x7fffffff;
+        for (int j = 1 + lane; j < count; j += 32) {
+            int idx = pos + j;
+            if (idx >= count) idx -= count;
+            short2 pt = src[idx];
+            double dx = pt.x - start_pt.x, dy = pt.y - start_pt.y;
+            double dist = dx * dx + dy * dy;
+            if (dist > best) { best = dist; bj = j; }
+        }
+        warp_argmax_first(best, bj);
+        if (best > 0) right.x = bj;
+        le_eps = best <= eps;
+    }
+    if (!le_eps) {
+        right.y = slice.x = pos % count;
+        slice.y = right.x = (right.x + slice.x) % count;
+        if (lane == 0) { stack[0] = right; stack[1] = slice; }
+        top = 2;
+    } else {
+        if (lane == 0) dst[0] = start_pt;
+        new_count = 1;
+    }
+    __syncwarp();
+    while (top > 0) {
+        slice = stack[--top];
+        end_pt = src[slice.y];
+        start_pt = src[slice.x];
+        int first = slice.x + 1;
+        if (first >= count) first = 0;
+        if (first != slice.y) {
+            int m = slice.y - first;           // elements first .. slice.y-1, circular
+            if (m < 0) m += count;
+            double dx = end_pt.x - start_pt.x, dy = end_pt.y - start_pt.y;
+            double L = dx * dx + dy * dy, best = 0;
+            int bt = 0x7fffffff;
+            for (int t = lane; t < m; t += 32) {
+                int idx = first + t;
+                if (idx >= count) idx -= count;
+                short2 pt = src[idx];
+                double px = pt.x - start_pt.x, py = pt.y - start_pt.y;
+                double tt = px * dx + py * dy, dist;
+                if (tt <= 0) dist = (px * px + py * py) * L;
+                else if (tt >= L) { double qx = pt.x - end_pt.x, qy = pt.y - end_pt.y; dist = (qx * qx + qy * qy) * L; }
+                else { double cr = py * dx - px * dy; dist = cr * cr; }
+                if (dist > best) { best = dist; bt = t; }
+            }
+            warp_argmax_first(best, bt);
+            if (best > 0) { int idx = first + bt; right.x = idx >= count ? idx - count : idx; }
+            le_eps = best <= eps * L;
+        } else {
+            le_eps = true;
+        }
+        __syncwarp();  // everyone has read stack[top] before it may be overwritten
+        if (le_eps) {
+            if (lane == 0) dst[new_count] = start_pt;
+            new_count++;
+        } else {
+            right.y = slice.y;
+            slice.y = right.x;
+            if (lane == 0) { stack[top] = right; stack[top + 1] = slice; }
+            top += 2;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) new_count = approx_cleanup(dst, new_count, eps);
+    return __shfl_sync(0xffffffffu, new_count, 0);
+}
+
 struct QMeta {  // per frame, zeroed before every batch
-    int ncand, nstart, flags, nb;
+    int ncand, nstart, flags, nb, nlong, pad_[3];
 };
+constexpr int LONG_NP = 96;   // contours with more vertices are handled by a whole warp
+constexpr int MAXLONG = MANTIS_MAX_PTS / LONG_NP + 1;
 
 struct QuadArgs {
     const uint32_t* morph_bits;
@@ -264,6 +367,7 @@ struct QuadArgs {
     int* np;
     int* off;
     short* bylen;         // [n][MAXB] border indices, longest walk first
+    short* longl;         // [n][MAXLONG] borders with more than LONG_NP vertices
     short* an;            // [n][MAXB] approxPolyDP vertex count
     short2* quad;         // [n][MAXB][4]
     short2* pts;          // [n][MANTIS_MAX_PTS]
@@ -355,36 +459,49 @@ __global__ void __launch_bounds__(CNT) k_qcand(QuadArgs a)
 }
 
 // ---- 2. probe walks ------------------------------------------------------------------------
-__global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a)
+// Copies the frame's bit plane into shared memory when the launch reserved room for it
+// (use_smem), so that the serial walks pay shared-memory latency per step instead of L2's.
+__device__ __forceinline__ const uint32_t* stage_bits(const uint32_t* g, int words, bool use_smem)
 {
-    const int frame = blockIdx.y, i = blockIdx.x * CNT + threadIdx.x;
+    extern __shared__ uint32_t s_bits[];
+    if (!use_smem) return g;
+    for (int i = threadIdx.x; i < words; i += blockDim.x) s_bits[i] = __ldg(g + i);
+    __syncthreads();
+    return s_bits;
+}
+
+__global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a, int use_smem)
+{
+    const int frame = blockIdx.x;
     QMeta* meta = a.meta + frame;
-    if (i >= min(meta->ncand, MAXCAND)) return;
+    const int ncand = min(meta->ncand, MAXCAND);
     const int W = a.W, H = a.H;
     BitImg im;
-    im.bits = a.morph_bits + (size_t)frame * H * a.WW;
+    im.bits = stage_bits(a.morph_bits + (size_t)frame * H * a.WW, H * a.WW, use_smem);
     im.W = W; im.H = H; im.WW = a.WW;
-    const uint32_t cand = a.cand[(size_t)frame * MAXCAND + i];
-    const bool is_hole = cand >> 31;
-    const int y = (cand >> 15) & 0xffff, x = cand & 0x7fff;
-    int np, steps;
-    bool ok;
-    if (!is_hole) {
-        OuterProbe v{x, y, 0, 0};
-        ok = follow_border(im, x, y, false, v);
-        np = v.npts; steps = v.steps;
-    } else {
-        HoleProbe v{x, y, W, H, 0, 0};
-        ok = follow_border(im, x - 1, y, true, v);
-        np = v.npts; steps = v.steps;
+    for (int i = threadIdx.x; i < ncand; i += CNT) {
+        const uint32_t cand = a.cand[(size_t)frame * MAXCAND + i];
+        const bool is_hole = cand >> 31;
+        const int y = (cand >> 15) & 0xffff, x = cand & 0x7fff;
+        int np, steps;
+        bool ok;
+        if (!is_hole) {
+            OuterProbe v{x, y, 0, 0};
+            ok = follow_border(im, x, y, false, v);
+            np = v.npts; steps = v.steps;
+        } else {
+            HoleProbe v{x, y, W, H, 0, 0};
+            ok = follow_border(im, x - 1, y, true, v);
+            np = v.npts; steps = v.steps;
+        }
+        if (!ok) continue;
+        int k = atomicAdd(&meta->nstart, 1);
+        if (k >= MAXB) { atomicOr(&meta->flags, FRAME_FLAG_BORDER_OVERFLOW); continue; }
+        const size_t o = (size_t)frame * MAXB + k;
+        a.ukey[o] = ((uint32_t)(y * (W + 1) + x) << 1) | (is_hole ? 1u : 0u);
+        a.unp[o] = np;
+        a.usteps[o] = steps;
     }
-    if (!ok) return;
-    int k = atomicAdd(&meta->nstart, 1);
-    if (k >= MAXB) { atomicOr(&meta->flags, FRAME_FLAG_BORDER_OVERFLOW); return; }
-    const size_t o = (size_t)frame * MAXB + k;
-    a.ukey[o] = ((uint32_t)(y * (W + 1) + x) << 1) | (is_hole ? 1u : 0u);
-    a.unp[o] = np;
-    a.usteps[o] = steps;
 }
 
 // ---- 3. discovery order, point offsets, by-length order ---------------------------------------
@@ -420,6 +537,10 @@ __global__ void __launch_bounds__(CNT) k_qrank(QuadArgs a)
         int r = 0;  // position by descending walk length (ties by index)
         for (int j = 0; j < nb; ++j) r += (s_st[j] > st) || (s_st[j] == st && j < i);
         a.bylen[base + r] = (short)i;
+        if (s_np[i] > LONG_NP) {
+            int k = atomicAdd(&meta->nlong, 1);
+            if (k < MAXLONG) a.longl[(size_t)frame * MAXLONG + k] = (short)i;
+        }
     }
 }
 
@@ -445,10 +566,36 @@ __global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a)
     int2* stack = a.stack + (size_t)frame * (MANTIS_MAX_PTS + 2 * MAXB) + off + 2 * b;
     Emit v{pts, a.owner + (size_t)frame * W * H, W, 0, (uint16_t)b};
     follow_border(im, is_hole ? x - 1 : x, y, is_hole, v);
+    if (np > LONG_NP) return;  // approximated by a whole warp in k_qapprox_long
     const int n4 = approx_poly_closed(pts, np, a.eps, dst, stack);
     a.an[base + b] = (short)min(n4, 32767);
     if (n4 == 4)
         for (int q = 0; q < 4; ++q) a.quad[(base + b) * 4 + q] = dst[q];
+}
+
+// long contours: approxPolyDP by a whole warp
+constexpr int LWARPS = 4;
+__global__ void __launch_bounds__(32 * LWARPS) k_qapprox_long(QuadArgs a)
+{
+    const int frame = blockIdx.x, lane = threadIdx.x & 31;
+    const QMeta* meta = a.meta + frame;
+    const int nlong = min(meta->nlong, MAXLONG);
+    if (meta->flags || nlong == 0) return;
+    const size_t base = (size_t)frame * MAXB;
+    for (int k = threadIdx.x >> 5; k < nlong; k += LWARPS) {
+        const int b = a.longl[(size_t)frame * MAXLONG + k];
+        const int off = a.off[base + b], np = a.np[base + b];
+        short2* pts = a.pts + (size_t)frame * MANTIS_MAX_PTS + off;
+        short2* dst = a.dst + (size_t)frame * MANTIS_MAX_PTS + off;
+        int2* stack = a.stack + (size_t)frame * (MANTIS_MAX_PTS + 2 * MAXB) + off + 2 * b;
+        const int n4 = approx_poly_closed_warp(pts, np, a.eps, dst, stack);
+        if (lane == 0) {
+            a.an[base + b] = (short)min(n4, 32767);
+            if (n4 == 4)
+                for (int q = 0; q < 4; ++q) a.quad[(base + b) * 4 + q] = dst[q];
+        }
+        __syncwarp();
+    }
 }
 
 // ---- 5. hole parents, CCOMP order, quads, de-duplication, output (per frame) --------------------
@@ -600,7 +747,7 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
     const size_t o_meta = take((size_t)n * sizeof(QMeta)), o_cand = take((size_t)n * MAXCAND * 4), o_ukey = take(nB * 4),
                  o_unp = take(nB * 4), o_ust = take(nB * 4), o_key = take(nB * 4), o_np = take(nB * 4), o_off = take(nB * 4),
-                 o_bylen = take(nB * 2), o_an = take(nB * 2), o_quad = take(nB * 4 * sizeof(short2));
+                 o_bylen = take(nB * 2), o_long = take((size_t)n * MAXLONG * 2), o_an = take(nB * 2), o_quad = take(nB * 4 * sizeof(short2));
     if ((rc = ctx_reserve(c, c->q_stack, o)) ||
         (rc = ctx_reserve(c, c->q_pts, (size_t)n * MANTIS_MAX_PTS * sizeof(short2) * 2)) ||
         (rc = ctx_reserve(c, c->q_dst, (size_t)n * (MANTIS_MAX_PTS + 2 * MAXB) * sizeof(int2))) ||
@@ -612,7 +759,7 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     a.W = w; a.H = h; a.WW = words_per_row(w); a.n_frames = n;
     a.meta = (QMeta*)(ar + o_meta); a.cand = (uint32_t*)(ar + o_cand); a.ukey = (uint32_t*)(ar + o_ukey);
     a.unp = (int*)(ar + o_unp); a.usteps = (int*)(ar + o_ust); a.key = (uint32_t*)(ar + o_key);
-    a.np = (int*)(ar + o_np); a.off = (int*)(ar + o_off); a.bylen = (short*)(ar + o_bylen);
+    a.np = (int*)(ar + o_np); a.off = (int*)(ar + o_off); a.bylen = (short*)(ar + o_bylen); a.longl = (short*)(ar + o_long);
     a.an = (short*)(ar + o_an); a.quad = (short2*)(ar + o_quad);
     a.pts = (short2*)c->q_pts.p;
     a.dst = a.pts + (size_t)n * MANTIS_MAX_PTS;
@@ -625,11 +772,17 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     MCHECK(c, cudaMemsetAsync(a.meta, 0, (size_t)n * sizeof(QMeta), c->stream));
     const int words = h * a.WW;
     k_qcand<<<dim3((words + CNT - 1) / CNT, n), CNT, 0, c->stream>>>(a);
-    k_qprobe<<<dim3(MAXCAND / CNT, n), CNT, 0, c->stream>>>(a);
+    const size_t plane = (size_t)words * sizeof(uint32_t);
+    const int use_smem = plane <= 200 * 1024;
+    if (use_smem) {
+        MCHECK(c, cudaFuncSetAttribute(k_qprobe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
+    }
+    k_qprobe<<<n, CNT, use_smem ? plane : 0, c->stream>>>(a, use_smem);
     k_qrank<<<n, CNT, 0, c->stream>>>(a);
     k_qtrace<<<dim3(MAXB / TNT, n), TNT, 0, c->stream>>>(a);
+    k_qapprox_long<<<n, 32 * LWARPS, 0, c->stream>>>(a);
     k_qfinish<<<n, FNT, 0, c->stream>>>(a);
-    c->launches += 5;
+    c->launches += 6;
     MCHECK(c, cudaGetLastError());
     return MANTIS_OK;
 }
