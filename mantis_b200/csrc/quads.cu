@@ -64,6 +64,25 @@ struct BitImg {
     }
 };
 
+// The same plane staged in shared memory with a zero frame: one zero row above and below, one
+// zero word left and right of every row (stride = WW + 2 words).  No bounds checks, no branches:
+// the three neighbourhood rows are funnel shifts of two adjacent words each.
+struct PadImg {
+    const uint32_t* base;  // word (row -1, word -1) of the padded plane
+    int stride;
+    __device__ __forceinline__ uint32_t nbr(int x, int y) const
+    {
+        const int xm = x + 31;  // column x-1 in padded coordinates
+        const uint32_t* p = base + (y + 1) * stride + (xm >> 5);
+        const int b = xm & 31;
+        const uint32_t up = __funnelshift_r(p[-stride], p[-stride + 1], b) & 7u;
+        const uint32_t mid = __funnelshift_r(p[0], p[1], b) & 7u;
+        const uint32_t dn = __funnelshift_r(p[stride], p[stride + 1], b) & 7u;
+        // up: NW N NE, mid: W . E, dn: SW S SE  ->  direction order E NE N NW W SW S SE
+        return (mid >> 2) | ((up & 4u) >> 1) | ((up & 2u) << 1) | ((up & 1u) << 3) | ((mid & 1u) << 4) | (dn << 5);
+    }
+};
+
 __device__ __forceinline__ int dir_dx(int s) { return (int)((0x901Au >> (2 * s)) & 3u) - 1; }
 __device__ __forceinline__ int dir_dy(int s) { return (int)((0xA901u >> (2 * s)) & 3u) - 1; }
 
@@ -72,8 +91,8 @@ __device__ __forceinline__ int dir_dy(int s) { return (int)((0xA901u >> (2 * s))
 //           examined as background from it; return false to abort.
 //           void point(x, y)        -- CHAIN_APPROX_SIMPLE vertex.
 // Returns true if the loop closed.
-template <class V>
-__device__ bool follow_border(const BitImg& im, int x0, int y0, bool is_hole, V& vis)
+template <class Img, class V>
+__device__ __forceinline__ bool follow_border(const Img& im, int x0, int y0, bool is_hole, V& vis)
 {
     const int s_end = is_hole ? 0 : 4;
     uint32_t nb = im.nbr(x0, y0);
@@ -459,26 +478,28 @@ __global__ void __launch_bounds__(CNT) k_qcand(QuadArgs a)
 }
 
 // ---- 2. probe walks ------------------------------------------------------------------------
-// Copies the frame's bit plane into shared memory when the launch reserved room for it
-// (use_smem), so that the serial walks pay shared-memory latency per step instead of L2's.
-__device__ __forceinline__ const uint32_t* stage_bits(const uint32_t* g, int words, bool use_smem)
+// Stages the frame's bit plane, zero-framed, in shared memory (PadImg layout).
+__device__ __forceinline__ PadImg stage_padded(const uint32_t* g, int H, int WW)
 {
     extern __shared__ uint32_t s_bits[];
-    if (!use_smem) return g;
-    for (int i = threadIdx.x; i < words; i += blockDim.x) s_bits[i] = __ldg(g + i);
+    const int stride = WW + 2, total = (H + 2) * stride;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int r = i / stride, cidx = i - r * stride;
+        s_bits[i] = (r >= 1 && r <= H && cidx >= 1 && cidx <= WW) ? __ldg(g + (size_t)(r - 1) * WW + (cidx - 1)) : 0u;
+    }
     __syncthreads();
-    return s_bits;
+    PadImg im;
+    im.base = s_bits;
+    im.stride = stride;
+    return im;
 }
 
-__global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a, int use_smem)
+template <class Img>
+__device__ __forceinline__ void probe_frame(const QuadArgs& a, const Img& im, int frame)
 {
-    const int frame = blockIdx.x;
     QMeta* meta = a.meta + frame;
     const int ncand = min(meta->ncand, MAXCAND);
     const int W = a.W, H = a.H;
-    BitImg im;
-    im.bits = stage_bits(a.morph_bits + (size_t)frame * H * a.WW, H * a.WW, use_smem);
-    im.W = W; im.H = H; im.WW = a.WW;
     for (int i = threadIdx.x; i < ncand; i += CNT) {
         const uint32_t cand = a.cand[(size_t)frame * MAXCAND + i];
         const bool is_hole = cand >> 31;
@@ -501,6 +522,19 @@ __global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a, int use_smem)
         a.ukey[o] = ((uint32_t)(y * (W + 1) + x) << 1) | (is_hole ? 1u : 0u);
         a.unp[o] = np;
         a.usteps[o] = steps;
+    }
+}
+
+__global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a, int use_smem)
+{
+    const int frame = blockIdx.x;
+    const uint32_t* g = a.morph_bits + (size_t)frame * a.H * a.WW;
+    if (use_smem) {
+        probe_frame(a, stage_padded(g, a.H, a.WW), frame);
+    } else {
+        BitImg im;
+        im.bits = g; im.W = a.W; im.H = a.H; im.WW = a.WW;
+        probe_frame(a, im, frame);
     }
 }
 
@@ -545,32 +579,45 @@ __global__ void __launch_bounds__(CNT) k_qrank(QuadArgs a)
 }
 
 // ---- 4. extraction + approxPolyDP, one thread per border --------------------------------------
-constexpr int TNT = 64;
-__global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a)
+constexpr int TNT = 256;
+template <class Img>
+__device__ __forceinline__ void trace_frame(const QuadArgs& a, const Img& im, int frame)
 {
-    const int frame = blockIdx.y, slot = blockIdx.x * TNT + threadIdx.x;
     const QMeta* meta = a.meta + frame;
-    if (meta->flags || slot >= meta->nb) return;
-    const int W = a.W, H = a.H;
+    if (meta->flags) return;
+    const int nb = meta->nb, W = a.W, H = a.H;
     const size_t base = (size_t)frame * MAXB;
-    const int b = a.bylen[base + slot];
-    BitImg im;
-    im.bits = a.morph_bits + (size_t)frame * H * a.WW;
-    im.W = W; im.H = H; im.WW = a.WW;
-    const uint32_t k = a.key[base + b];
-    const bool is_hole = k & 1u;
-    const int p = (int)(k >> 1), y = p / (W + 1), x = p - y * (W + 1);
-    const int off = a.off[base + b], np = a.np[base + b];
-    short2* pts = a.pts + (size_t)frame * MANTIS_MAX_PTS + off;
-    short2* dst = a.dst + (size_t)frame * MANTIS_MAX_PTS + off;
-    int2* stack = a.stack + (size_t)frame * (MANTIS_MAX_PTS + 2 * MAXB) + off + 2 * b;
-    Emit v{pts, a.owner + (size_t)frame * W * H, W, 0, (uint16_t)b};
-    follow_border(im, is_hole ? x - 1 : x, y, is_hole, v);
-    if (np > LONG_NP) return;  // approximated by a whole warp in k_qapprox_long
-    const int n4 = approx_poly_closed(pts, np, a.eps, dst, stack);
-    a.an[base + b] = (short)min(n4, 32767);
-    if (n4 == 4)
-        for (int q = 0; q < 4; ++q) a.quad[(base + b) * 4 + q] = dst[q];
+    for (int slot = threadIdx.x; slot < nb; slot += TNT) {
+        const int b = a.bylen[base + slot];
+        const uint32_t k = a.key[base + b];
+        const bool is_hole = k & 1u;
+        const int p = (int)(k >> 1), y = p / (W + 1), x = p - y * (W + 1);
+        const int off = a.off[base + b], np = a.np[base + b];
+        short2* pts = a.pts + (size_t)frame * MANTIS_MAX_PTS + off;
+        short2* dst = a.dst + (size_t)frame * MANTIS_MAX_PTS + off;
+        int2* stack = a.stack + (size_t)frame * (MANTIS_MAX_PTS + 2 * MAXB) + off + 2 * b;
+        Emit v{pts, a.owner + (size_t)frame * W * H, W, 0, (uint16_t)b};
+        follow_border(im, is_hole ? x - 1 : x, y, is_hole, v);
+        if (np > LONG_NP) continue;  // approximated by a whole warp in k_qapprox_long
+        const int n4 = approx_poly_closed(pts, np, a.eps, dst, stack);
+        a.an[base + b] = (short)min(n4, 32767);
+        if (n4 == 4)
+            for (int q = 0; q < 4; ++q) a.quad[(base + b) * 4 + q] = dst[q];
+    }
+}
+
+__global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a, int use_smem)
+{
+    const int frame = blockIdx.x;
+    const uint32_t* g = a.morph_bits + (size_t)frame * a.H * a.WW;
+    if (use_smem) {
+        if (a.meta[frame].flags || a.meta[frame].nb == 0) return;
+        trace_frame(a, stage_padded(g, a.H, a.WW), frame);
+    } else {
+        BitImg im;
+        im.bits = g; im.W = a.W; im.H = a.H; im.WW = a.WW;
+        trace_frame(a, im, frame);
+    }
 }
 
 // long contours: approxPolyDP by a whole warp
@@ -772,14 +819,15 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     MCHECK(c, cudaMemsetAsync(a.meta, 0, (size_t)n * sizeof(QMeta), c->stream));
     const int words = h * a.WW;
     k_qcand<<<dim3((words + CNT - 1) / CNT, n), CNT, 0, c->stream>>>(a);
-    const size_t plane = (size_t)words * sizeof(uint32_t);
+    const size_t plane = (size_t)(h + 2) * (a.WW + 2) * sizeof(uint32_t);
     const int use_smem = plane <= 200 * 1024;
     if (use_smem) {
         MCHECK(c, cudaFuncSetAttribute(k_qprobe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
+        MCHECK(c, cudaFuncSetAttribute(k_qtrace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
     }
     k_qprobe<<<n, CNT, use_smem ? plane : 0, c->stream>>>(a, use_smem);
     k_qrank<<<n, CNT, 0, c->stream>>>(a);
-    k_qtrace<<<dim3(MAXB / TNT, n), TNT, 0, c->stream>>>(a);
+    k_qtrace<<<n, TNT, use_smem ? plane : 0, c->stream>>>(a, use_smem);
     k_qapprox_long<<<n, 32 * LWARPS, 0, c->stream>>>(a);
     k_qfinish<<<n, FNT, 0, c->stream>>>(a);
     c->launches += 6;
