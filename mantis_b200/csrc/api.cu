@@ -72,7 +72,7 @@ int mantis_destroy(mantis_ctx* c)
     if (!c) return MANTIS_ERR_INVALID;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_out0,
+    DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_in2, &c->stage_out0,
                       &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->frame_quads,
                       &c->cams, &c->hyps, &c->sel, &c->pose_info, &c->results, &c->traces, &c->mask_bits,
                       &c->d_map, &c->d_rand, &c->d_shifts, &c->render_poses, &c->quad_hyp, &c->pose_offs};
@@ -82,6 +82,11 @@ int mantis_destroy(mantis_ctx* c)
     if (c->pin_out) cudaFreeHost(c->pin_out);
     for (int i = 0; i <= MANTIS_N_STAGES; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for (int i = 0; i < 2; ++i) {
+        if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
+        if (c->ev_free[i]) cudaEventDestroy(c->ev_free[i]);
+    }
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     cudaStreamDestroy(c->stream);
     delete c;
     return MANTIS_OK;

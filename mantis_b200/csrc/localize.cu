@@ -1,6 +1,7 @@
 // localize.cu -- mantis_localize_batch(): the whole quadDetection() callback (src/mantis3.cpp:68-135)
 // for a batch of frames, plus the per-context tables it needs (world map, refinement
 // perturbations, cell shifts).
+#include <stdlib.h>
 #include <new>
 #include <vector>
 #include "ctx.h"
@@ -108,7 +109,13 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     }
     MCHECK(c, cudaSetDevice(c->device));
 
-    const int CHUNK = 512;
+    // frames per pass of the kernel chain: large enough that the latency-bound tails (longest border
+    // walk, slowest RPP run) are amortised over many frames, small enough that the per-frame scratch
+    // (about 1.8 MB at 640x480, dominated by the contour buffers) stays within a few GB
+    static const int chunk_env = []() { const char* e = getenv("MANTIS_CHUNK"); return e ? atoi(e) : 0; }();
+    int CHUNK = chunk_env > 0 ? chunk_env : (int)(4096.0 * (640.0 * 480.0) / ((double)W * H));
+    if (chunk_env <= 0) CHUNK = CHUNK < 256 ? 256 : CHUNK > 4096 ? 4096 : CHUNK;
+    if (mem == MANTIS_MEM_HOST && chunk_env <= 0 && CHUNK > 1024) CHUNK = 1024;  // finer grain for the copy/compute overlap
     const int WW = words_per_row(W);
     const int nc_max = n < CHUNK ? n : CHUNK;
     const size_t plane_bytes = (size_t)nc_max * H * WW * sizeof(uint32_t);
@@ -123,22 +130,53 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         (rc = ctx_reserve(c, c->results, (size_t)nc_max * sizeof(mantis_result))) ||
         (rc = ctx_reserve(c, c->traces, (size_t)nc_max * sizeof(mantis_frame_trace))))
         return rc;
-    if (mem == MANTIS_MEM_HOST && (rc = ctx_reserve(c, c->stage_in, (size_t)nc_max * 3 * W * H))) return rc;
+    // Host-resident frames: chunks are staged through two device buffers on a copy stream, so the
+    // H2D transfer of chunk k+1 overlaps the kernels of chunk k.
+    const bool host = mem == MANTIS_MEM_HOST;
+    const size_t tight = (size_t)3 * W * H;
+    bool contiguous = host && stride0 == 3 * W;
+    if (host) {
+        for (int i = 1; i < n && contiguous; ++i) contiguous = frames[i].bgr == frames[0].bgr + (size_t)i * tight;
+        if ((rc = ctx_reserve(c, c->stage_in, (size_t)nc_max * tight)) ||
+            (n > CHUNK && (rc = ctx_reserve(c, c->stage_in2, (size_t)nc_max * tight))))
+            return rc;
+        if (!c->copy_stream) {
+            MCHECK(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+            for (int i = 0; i < 2; ++i) {
+                MCHECK(c, cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
+                MCHECK(c, cudaEventCreateWithFlags(&c->ev_free[i], cudaEventDisableTiming));
+            }
+        }
+    }
+    auto issue_copy = [&](int k) -> int {
+        const int f0 = k * CHUNK, nc = (n - f0 < CHUNK) ? (n - f0) : CHUNK, buf = k & 1;
+        uint8_t* dst = (uint8_t*)(buf ? c->stage_in2.p : c->stage_in.p);
+        if (k >= 2) MCHECK(c, cudaStreamWaitEvent(c->copy_stream, c->ev_free[buf], 0));
+        if (contiguous) {
+            MCHECK(c, cudaMemcpyAsync(dst, frames[f0].bgr, (size_t)nc * tight, cudaMemcpyHostToDevice, c->copy_stream));
+        } else {
+            for (int i = 0; i < nc; ++i)
+                MCHECK(c, cudaMemcpy2DAsync(dst + (size_t)i * tight, 3 * W, frames[f0 + i].bgr, stride0, (size_t)3 * W, H,
+                                            cudaMemcpyHostToDevice, c->copy_stream));
+        }
+        MCHECK(c, cudaEventRecord(c->ev_copied[buf], c->copy_stream));
+        return MANTIS_OK;
+    };
+    if (host && (rc = issue_copy(0))) return rc;
 
     std::vector<pm::Camera> cams((size_t)nc_max);
-    for (int f0 = 0; f0 < n; f0 += CHUNK) {
+    for (int f0 = 0, k = 0; f0 < n; f0 += CHUNK, ++k) {
         const int nc = (n - f0 < CHUNK) ? (n - f0) : CHUNK;
         const uint8_t* d_in;
         size_t pitch;
         int stride;
         prof_mark(c, 0);
-        if (mem == MANTIS_MEM_HOST) {  // gather into a tightly packed device batch
+        if (host) {
+            if (f0 + CHUNK < n && (rc = issue_copy(k + 1))) return rc;
+            MCHECK(c, cudaStreamWaitEvent(c->stream, c->ev_copied[k & 1], 0));
             stride = 3 * W;
-            pitch = (size_t)stride * H;
-            for (int i = 0; i < nc; ++i)
-                MCHECK(c, cudaMemcpy2DAsync((uint8_t*)c->stage_in.p + (size_t)i * pitch, stride, frames[f0 + i].bgr, stride0,
-                                            (size_t)3 * W, H, cudaMemcpyHostToDevice, c->stream));
-            d_in = (const uint8_t*)c->stage_in.p;
+            pitch = tight;
+            d_in = (const uint8_t*)((k & 1) ? c->stage_in2.p : c->stage_in.p);
         } else {
             stride = stride0;
             pitch = dev_pitch;
@@ -171,6 +209,7 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
                                 trace ? (mantis_frame_trace*)c->traces.p : nullptr)))
             return rc;
         prof_mark(c, 6);
+        if (host) MCHECK(c, cudaEventRecord(c->ev_free[k & 1], c->stream));
         MCHECK(c, cudaMemcpyAsync(out + f0, c->results.p, sizeof(mantis_result) * (size_t)nc, cudaMemcpyDeviceToHost, c->stream));
         if (trace)
             MCHECK(c, cudaMemcpyAsync(trace + f0, c->traces.p, sizeof(mantis_frame_trace) * (size_t)nc,

@@ -8,6 +8,7 @@
 // batch (k_pose_run), for up to two corner orderings; passing quads emit four
 // yaw-rotated hypotheses in quad order.  The greedy Euler-space clustering is sequential over
 // seeds (as in the reference) and parallel over members.
+#include <stdlib.h>
 #include "ctx.h"
 #include "rpp_fast.cuh"
 
@@ -365,7 +366,8 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
     a.candR = (double*)(ws + o_cr); a.run2 = (RunOut*)(ws + o_run2);
     MCHECK(c, cudaMemsetAsync(a.cnt, 0, sizeof(PoseCounters), c->stream));
     k_pose_prep<<<n, PNT, 0, c->stream>>>(a);
-    const int run_blocks = c->sm_count * 4, flat_blocks = c->sm_count * 4;
+    static const int rb = []() { const char* e = getenv("MANTIS_RUN_BLOCKS"); int v = e ? atoi(e) : 0; return v > 0 ? v : 4; }();
+    const int run_blocks = c->sm_count * rb, flat_blocks = c->sm_count * 4;
     for (int round = 0; round < 2; ++round) {
         k_pose_run<false><<<run_blocks, RNT, 0, c->stream>>>(a, round);
         k_pose_second<<<flat_blocks, PNT, 0, c->stream>>>(a, round);

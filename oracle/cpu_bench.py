@@ -44,20 +44,20 @@ def _init(jobs):
 
 
 def _step(args):
-    key, stage = args[:5], args[5]
+    key, stage, reps = args[:5], args[5], args[6]
     from oracle import pyoracle as po
 
     frames, K, D = _FRAMES[key]
     ok = 0
     t0 = time.perf_counter()
-    for f in frames:
+    for f in frames * reps:
         if stage == "edges":
             po.edge_stage(f, 50)
             ok += 1
         else:
             tr, _m = po.localize(f, K, D)
             ok += tr.status == 0
-    return time.perf_counter() - t0, len(frames), ok
+    return time.perf_counter() - t0, len(frames) * reps, ok
 
 
 class CpuPath:
@@ -74,10 +74,11 @@ class CpuPath:
         self.pool.map(_prepare, self.jobs, chunksize=1)  # returns once the workers are up
         self.frames = frames_per_core * self.cores
 
-    def step(self, stage="localize"):
-        """Returns (wall seconds of the pass, frames processed, frames with status OK)."""
+    def step(self, stage="localize", reps=1):
+        """One pass (repeated `reps` times) over the sample.  Returns (wall seconds, frames processed,
+        frames with status OK)."""
         t0 = time.perf_counter()
-        res = self.pool.map(_step, [j + (stage,) for j in self.jobs], chunksize=1)
+        res = self.pool.map(_step, [j + (stage, reps) for j in self.jobs], chunksize=1)
         wall = time.perf_counter() - t0
         return wall, sum(r[1] for r in res), sum(r[2] for r in res)
 
