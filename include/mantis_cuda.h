@@ -136,6 +136,41 @@ int mantis_quads_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, in
                        int stride_bytes, size_t frame_pitch_bytes, mantis_frame_quads* out, int mem);
 
 /*
+ * Line voting on the stage's edge map (north-star stage "Hough / line-voting accumulator, line
+ * clustering, grid-intersection extraction").  The reference itself has no Hough transform -- its
+ * grid primitives are the cell quads of mantis_quads_batch (include/mantis3/QuadDetection.h:216-226) --
+ * so this entry point is not on the localization path.  Voting and peak picking follow
+ * cv::HoughLines(edges, rho = 1, theta = pi/180, threshold) of the OpenCV the reference links
+ * (accumulator (180+2) x (2(W+H)+1+2), 4-neighbour local maxima above threshold, strongest first,
+ * ties by accumulator index).  Clustering and intersections are defined by this library
+ * (oracle/hough.c states them): greedy (rho, theta) clustering around the strongest lines with
+ * vote-weighted means, then the crossings of the two dominant pencils that fall inside the image.
+ */
+#define MANTIS_HOUGH_MAX_LINES 1024
+#define MANTIS_HOUGH_MAX_CLUSTERS 256
+#define MANTIS_HOUGH_MAX_POINTS 1024
+enum { MANTIS_HOUGH_FLAG_PEAK_OVERFLOW = 1 };  /* more local maxima than the peak buffer holds (4096) */
+typedef struct mantis_hough_line { float rho, theta; int32_t votes; } mantis_hough_line;
+typedef struct mantis_hough_cluster { float rho, theta; int32_t votes, members; } mantis_hough_cluster;
+typedef struct mantis_frame_lines {
+    int32_t n_peaks;     /* local maxima above threshold (what cv::HoughLines would return) */
+    int32_t n_lines;     /* min(n_peaks, MANTIS_HOUGH_MAX_LINES) */
+    int32_t n_clusters, n_points, flags, pad_;
+    mantis_hough_line lines[MANTIS_HOUGH_MAX_LINES];
+    mantis_hough_cluster clusters[MANTIS_HOUGH_MAX_CLUSTERS];
+    float points[MANTIS_HOUGH_MAX_POINTS][2];
+} mantis_frame_lines;
+typedef struct mantis_hough_params {
+    int32_t threshold;     /* accumulator threshold (votes > threshold) */
+    int32_t use_morph;     /* 0: vote on the Canny map, 1: on the dilate x2 / erode x1 map */
+    double rho_tol;        /* clustering tolerances */
+    double theta_tol;
+    double pencil_tol;     /* angular half-width of a pencil */
+} mantis_hough_params;
+int mantis_hough_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                       size_t frame_pitch_bytes, const mantis_hough_params* prm, mantis_frame_lines* out, int mem);
+
+/*
  * Whole-frame localization: everything quadDetection() does between receiving the image and
  * calling publishPose() (src/mantis3.cpp:68-135).
  */

@@ -12,6 +12,7 @@ from .binding import (  # noqa: F401
     Config,
     Context,
     Frame,
+    FrameLines,
     FrameQuads,
     FrameTrace,
     Result,

@@ -80,6 +80,34 @@ class FrameTrace(ctypes.Structure):
                 ("shift_err", ctypes.c_double * 81), ("yaw_err", ctypes.c_double * 4)]
 
 
+HOUGH_MAX_LINES, HOUGH_MAX_CLUSTERS, HOUGH_MAX_POINTS = 1024, 256, 1024
+
+
+class HoughLine(ctypes.Structure):
+    _fields_ = [("rho", ctypes.c_float), ("theta", ctypes.c_float), ("votes", ctypes.c_int32)]
+
+
+class HoughCluster(ctypes.Structure):
+    _fields_ = [("rho", ctypes.c_float), ("theta", ctypes.c_float), ("votes", ctypes.c_int32),
+                ("members", ctypes.c_int32)]
+
+
+class FrameLines(ctypes.Structure):
+    """mantis_frame_lines."""
+
+    _fields_ = [("n_peaks", ctypes.c_int32), ("n_lines", ctypes.c_int32), ("n_clusters", ctypes.c_int32),
+                ("n_points", ctypes.c_int32), ("flags", ctypes.c_int32), ("pad_", ctypes.c_int32),
+                ("lines", HoughLine * HOUGH_MAX_LINES), ("clusters", HoughCluster * HOUGH_MAX_CLUSTERS),
+                ("points", (ctypes.c_float * 2) * HOUGH_MAX_POINTS)]
+
+
+class HoughParams(ctypes.Structure):
+    """mantis_hough_params."""
+
+    _fields_ = [("threshold", ctypes.c_int32), ("use_morph", ctypes.c_int32), ("rho_tol", ctypes.c_double),
+                ("theta_tol", ctypes.c_double), ("pencil_tol", ctypes.c_double)]
+
+
 def library_path():
     return os.path.join(_HERE, "libmantis_cuda.so")
 
@@ -123,6 +151,8 @@ def load_library():
                                       c.c_void_p, c.c_int]
     lib.mantis_quads_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
                                        c.c_void_p, c.c_int]
+    lib.mantis_hough_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
+                                       c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_set_map.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int]
     lib.mantis_localize_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_render_grid_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p,
@@ -235,6 +265,21 @@ class Context:
         out = (FrameQuads * n)()
         rc = self._lib.mantis_quads_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, ctypes.addressof(out), MEM_HOST)
         self._check(rc, "mantis_quads_batch")
+        return out
+
+    # -- line voting (north-star stage; cv::HoughLines semantics, no reference call site) --
+    def hough(self, bgr, threshold, use_morph=False, rho_tol=8.0, theta_tol=np.deg2rad(4.0),
+              pencil_tol=np.deg2rad(25.0)):
+        """Returns one FrameLines record per frame (peaks, clustered lines, pencil crossings)."""
+        bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, _ = bgr.shape
+        out = (FrameLines * n)()
+        prm = HoughParams(int(threshold), int(use_morph), float(rho_tol), float(theta_tol), float(pencil_tol))
+        rc = self._lib.mantis_hough_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, ctypes.byref(prm),
+                                          ctypes.addressof(out), MEM_HOST)
+        self._check(rc, "mantis_hough_batch")
         return out
 
     # -- quadDetection(), src/mantis3.cpp:68-135 --

@@ -75,7 +75,8 @@ int mantis_destroy(mantis_ctx* c)
     DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_in2, &c->stage_out0,
                       &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->frame_quads,
                       &c->cams, &c->hyps, &c->sel, &c->pose_info, &c->results, &c->traces, &c->mask_bits,
-                      &c->d_map, &c->d_rand, &c->d_shifts, &c->render_poses, &c->quad_hyp, &c->pose_offs};
+                      &c->d_map, &c->d_rand, &c->d_shifts, &c->render_poses, &c->quad_hyp, &c->pose_offs,
+                      &c->hough_trig, &c->hough_count, &c->hough_peaks, &c->hough_lines};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->pin_in) cudaFreeHost(c->pin_in);
@@ -130,8 +131,10 @@ const char* mantis_last_error(const mantis_ctx* c) { return c ? c->err : ""; }
 uint64_t mantis_launch_count(const mantis_ctx* c) { return c ? c->launches : 0; }
 void* mantis_stream(const mantis_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
+}  // extern "C"
+
 // ---- shared plumbing --------------------------------------------------------------------
-static int check_frames(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+int check_frames(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
                         size_t frame_pitch_bytes, int mem)
 {
     if (!c) return MANTIS_ERR_INVALID;
@@ -143,7 +146,7 @@ static int check_frames(mantis_ctx* c, const uint8_t* bgr, int n, int width, int
 }
 
 // Brings the frames onto the device if the caller holds them on the host.
-static int stage_input(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+int stage_input(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
                        size_t frame_pitch_bytes, int mem, const uint8_t** d_in)
 {
     *d_in = bgr;
@@ -187,6 +190,8 @@ int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int hei
     }
     return MANTIS_OK;
 }
+
+extern "C" {
 
 int mantis_edges_batch(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
                        size_t frame_pitch_bytes, uint8_t* canny_out, uint8_t* morph_out, int mem)

@@ -34,6 +34,7 @@ struct mantis_ctx {
     DevBuf quad_hyp, pose_offs;
     DevBuf cams, hyps, sel, pose_info, results, traces, mask_bits;  // localize scratch (per chunk)
     DevBuf render_poses;
+    DevBuf hough_trig, hough_count, hough_peaks, hough_lines;  // line-voting stage (hough.cu)
     DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts
     int n_map = 0, n_green = 0, n_shift = 0;
     Tf rotz;                                 // +90 degrees about z
@@ -113,5 +114,11 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
                   const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace);
 extern "C" int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int height, int stride_bytes,
                    size_t frame_pitch_bytes, const EdgeOutputs& out);
+
+// argument validation / host->device staging shared by the stage entry points (api.cu)
+int check_frames(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                 size_t frame_pitch_bytes, int mem);
+int stage_input(mantis_ctx* c, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                size_t frame_pitch_bytes, int mem, const uint8_t** d_in);
 
 static inline int words_per_row(int w) { return (w + 31) >> 5; }

@@ -101,3 +101,111 @@ int mo_hough_lines(const uint8_t* edges, int w, int h, double rho, double theta,
     free(sort_buf); free(accum); free(tab_sin); free(tab_cos);
     return n_out;
 }
+
+/* ---- line clustering and grid intersections (defined by this repo; no third-party counterpart) ----
+ *
+ * Lines arrive strongest first.  Greedy clustering: a line joins the first earlier seed it is similar
+ * to, else it becomes a seed.  Similar: |d theta| <= theta_tol and |d rho| <= rho_tol, where a line
+ * more than pi/2 away in angle is first re-expressed as (-rho, theta -+ pi).  A cluster's line is the
+ * vote-weighted mean of its members, accumulated in integers (2*rho and the angle index are integers
+ * for rho = 1), so the result does not depend on summation order. */
+typedef struct mo_hough_cluster {
+    float rho, theta;
+    int votes, members;
+} mo_hough_cluster;
+
+int mo_hough_cluster_lines(const mo_hough_line* lines, int n, double theta_step, int numangle, double rho_tol,
+                           double theta_tol, mo_hough_cluster* out, int max_clusters)
+{
+    int* seed_of = (int*)malloc(sizeof(int) * (n > 0 ? n : 1));
+    int nc = 0;
+    long long* s_v = (long long*)calloc(max_clusters, sizeof(long long));
+    long long* s_r = (long long*)calloc(max_clusters, sizeof(long long));
+    long long* s_a = (long long*)calloc(max_clusters, sizeof(long long));
+    int* seed_idx = (int*)malloc(sizeof(int) * max_clusters);
+    int* members = (int*)calloc(max_clusters, sizeof(int));
+    for (int i = 0; i < n; i++) {
+        int ai = (int)lrint(lines[i].theta / (float)theta_step);  /* angle index */
+        long long r2 = (long long)lrint(2.0 * lines[i].rho);
+        int c_found = -1, a_use = ai;
+        long long r_use = r2;
+        for (int c = 0; c < nc; c++) {
+            const mo_hough_line* s = &lines[seed_idx[c]];
+            int as = (int)lrint(s->theta / (float)theta_step);
+            long long rs2 = (long long)lrint(2.0 * s->rho);
+            int a = ai;
+            long long r = r2;
+            if (abs(a - as) * 2 > numangle) { a = a > as ? a - numangle : a + numangle; r = -r; }
+            if (fabs((double)(a - as)) * theta_step <= theta_tol && fabs((double)(r - rs2)) * 0.5 <= rho_tol) {
+                c_found = c; a_use = a; r_use = r;
+                break;
+            }
+        }
+        if (c_found < 0) {
+            if (nc >= max_clusters) { seed_of[i] = -1; continue; }
+            c_found = nc++;
+            seed_idx[c_found] = i;
+        }
+        seed_of[i] = c_found;
+        s_v[c_found] += lines[i].votes;
+        s_r[c_found] += (long long)lines[i].votes * r_use;
+        s_a[c_found] += (long long)lines[i].votes * a_use;
+        members[c_found]++;
+    }
+    for (int c = 0; c < nc; c++) {
+        out[c].rho = (float)((double)s_r[c] / (2.0 * (double)s_v[c]));
+        out[c].theta = (float)(((double)s_a[c] / (double)s_v[c]) * theta_step);
+        out[c].votes = (int)s_v[c];
+        out[c].members = members[c];
+    }
+    free(seed_of); free(s_v); free(s_r); free(s_a); free(seed_idx); free(members);
+    return nc;
+}
+
+/* Two dominant pencils: A = clusters within pencil_tol (mod pi) of the strongest cluster's angle,
+ * B = clusters within pencil_tol of the strongest cluster that is at least pi/4 away from A's.
+ * Intersections of every (a in A, b in B) pair, a-major in cluster order, kept when inside the
+ * image.  xy receives (x, y) float pairs; pencil (optional, n entries) receives 0 = A, 1 = B, -1. */
+static double ang_dist(double a, double b)
+{
+    double d = fabs(a - b);
+    d = fmod(d, MO_PI);
+    return d > MO_PI / 2 ? MO_PI - d : d;
+}
+
+int mo_hough_intersections(const mo_hough_cluster* cl, int n, int w, int h, double pencil_tol, float* xy,
+                           int max_points, int* pencil)
+{
+    int* pen = (int*)malloc(sizeof(int) * (n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) pen[i] = -1;
+    int count = 0;
+    if (n > 0) {
+        int sa = 0, sb = -1;
+        for (int i = 1; i < n; i++)
+            if (cl[i].votes > cl[sa].votes) sa = i;
+        for (int i = 0; i < n; i++)
+            if (ang_dist(cl[i].theta, cl[sa].theta) >= MO_PI / 4 && (sb < 0 || cl[i].votes > cl[sb].votes)) sb = i;
+        for (int i = 0; i < n; i++) {
+            if (ang_dist(cl[i].theta, cl[sa].theta) <= pencil_tol) pen[i] = 0;
+            else if (sb >= 0 && ang_dist(cl[i].theta, cl[sb].theta) <= pencil_tol) pen[i] = 1;
+        }
+        for (int a = 0; a < n; a++) {
+            if (pen[a] != 0) continue;
+            double ca = cos((double)cl[a].theta), sna = sin((double)cl[a].theta);
+            for (int b = 0; b < n; b++) {
+                if (pen[b] != 1) continue;
+                double cb = cos((double)cl[b].theta), snb = sin((double)cl[b].theta);
+                double det = ca * snb - sna * cb;
+                if (fabs(det) < 1e-9) continue;
+                double x = ((double)cl[a].rho * snb - (double)cl[b].rho * sna) / det;
+                double y = ((double)cl[b].rho * ca - (double)cl[a].rho * cb) / det;
+                if (!(x >= 0 && x < w && y >= 0 && y < h)) continue;
+                if (count < max_points) { xy[2 * count] = (float)x; xy[2 * count + 1] = (float)y; }
+                count++;
+            }
+        }
+    }
+    if (pencil) memcpy(pencil, pen, sizeof(int) * n);
+    free(pen);
+    return count < max_points ? count : max_points;
+}

@@ -292,3 +292,66 @@ def render_grid(R_w2c, t_w2c, K, D, w, h, line_width=0.04, floor_level=30):
     f.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_void_p]
     f(_dp(R), _dp(t), _dp(K), _dp(D), w, h, float(line_width), int(floor_level), _dp(out))
     return out
+
+
+# ---- Hough (row a6'; cv::HoughLines semantics, see oracle/hough.c) ----
+class HoughLine(ctypes.Structure):
+    _fields_ = [("rho", ctypes.c_float), ("theta", ctypes.c_float), ("votes", ctypes.c_int)]
+
+
+def hough_dims(w, h, rho=1.0, theta=np.pi / 180):
+    na, nr = ctypes.c_int(), ctypes.c_int()
+    f = lib().mo_hough_dims
+    f.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
+    f(w, h, float(rho), float(theta), ctypes.byref(na), ctypes.byref(nr))
+    return na.value, nr.value
+
+
+def hough_lines(edges, threshold, rho=1.0, theta=np.pi / 180, max_lines=4096, want_accum=False):
+    """Returns (lines [n,3] float64 of rho, theta, votes) and optionally the accumulator."""
+    edges, p = _u8(edges)
+    h, w = edges.shape
+    out = (HoughLine * max_lines)()
+    na, nr = hough_dims(w, h, rho, theta)
+    acc = np.zeros((na + 2, nr + 2), np.int32) if want_accum else None
+    f = lib().mo_hough_lines
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_int,
+                  ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    n = f(p, w, h, float(rho), float(theta), int(threshold), ctypes.addressof(out), max_lines,
+          acc.ctypes.data if want_accum else None)
+    lines = np.array([[out[i].rho, out[i].theta, out[i].votes] for i in range(n)], np.float64).reshape(n, 3)
+    return (lines, acc) if want_accum else lines
+
+
+class HoughCluster(ctypes.Structure):
+    _fields_ = [("rho", ctypes.c_float), ("theta", ctypes.c_float), ("votes", ctypes.c_int), ("members", ctypes.c_int)]
+
+
+def hough_clusters(lines, w, h, rho_tol=8.0, theta_tol=np.deg2rad(4.0), theta=np.pi / 180, max_clusters=256):
+    """lines: [n,3] (rho, theta, votes) strongest first -> [m,4] (rho, theta, votes, members)."""
+    n = len(lines)
+    arr = (HoughLine * max(n, 1))()
+    for i in range(n):
+        arr[i].rho, arr[i].theta, arr[i].votes = float(lines[i][0]), float(lines[i][1]), int(lines[i][2])
+    out = (HoughCluster * max_clusters)()
+    na, _ = hough_dims(w, h, 1.0, theta)
+    f = lib().mo_hough_cluster_lines
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                  ctypes.c_void_p, ctypes.c_int]
+    m = f(ctypes.addressof(arr), n, float(theta), na, float(rho_tol), float(theta_tol), ctypes.addressof(out), max_clusters)
+    return np.array([[out[i].rho, out[i].theta, out[i].votes, out[i].members] for i in range(m)], np.float64).reshape(m, 4)
+
+
+def hough_intersections(clusters, w, h, pencil_tol=np.deg2rad(25.0), max_points=1024):
+    n = len(clusters)
+    arr = (HoughCluster * max(n, 1))()
+    for i in range(n):
+        arr[i].rho, arr[i].theta = float(clusters[i][0]), float(clusters[i][1])
+        arr[i].votes, arr[i].members = int(clusters[i][2]), int(clusters[i][3])
+    xy = np.zeros((max_points, 2), np.float32)
+    pen = np.zeros(max(n, 1), np.int32)
+    f = lib().mo_hough_intersections
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_void_p,
+                  ctypes.c_int, ctypes.c_void_p]
+    m = f(ctypes.addressof(arr), n, w, h, float(pencil_tol), xy.ctypes.data, max_points, pen.ctypes.data)
+    return xy[:m].copy(), pen[:n].copy()
