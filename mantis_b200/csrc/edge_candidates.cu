@@ -125,10 +125,10 @@ __device__ __forceinline__ void sobel_march(Tile& s, int x0, int y0, int W, int 
     int sa[4], da[4], sb[4], db[4], sc[4], dc[4];
     hrow_sobel(s.blur[r0][lw - 1], s.blur[r0][lw], s.blur[r0][lw + 1], sa, da);
     hrow_sobel(s.blur[r0 + 1][lw - 1], s.blur[r0 + 1][lw], s.blur[r0 + 1][lw + 1], sb, db);
-#pragma unroll
-    for (int r = 0; r < RPW; ++r) {
+    const int nr = min(RPW, DH - r0);  // 9, 9, 9, 7: warp-uniform
+#pragma unroll 3
+    for (int r = 0; r < nr; ++r) {
         const int ld = r0 + r;  // dxdy row ld <-> image row y0 - 1 + ld, needs blur rows ld .. ld+2
-        if (ld >= DH) break;    // warp-uniform (only the last warp stops early)
         hrow_sobel(s.blur[ld + 2][lw - 1], s.blur[ld + 2][lw], s.blur[ld + 2][lw + 1], sc, dc);
         int dx[4], dy[4];
 #pragma unroll
@@ -188,36 +188,41 @@ k_edge_candidates(const uint8_t* __restrict__ bgr, int W, int H, int stride, siz
 
     // ---- phase 0: gray words ----
     if (vec_ok) {
-        // Every word is computed from a legal, clamped address (loads first, in two batches, so that
-        // each thread has up to 18 requests in flight); words outside the image hold garbage until the
-        // ring pass below fills the one-pixel frame that in-image outputs actually read.
-        int ly = tid / GWW, lw = tid - ly * GWW;
+        // Every word is computed from a legal, clamped address; words outside the image hold garbage
+        // until the ring pass below fills the one-pixel frame that in-image outputs actually read.
+        // Lane l owns word column 1 + l; warp w takes rows w, w+4, ...; loads are issued five rows at
+        // a time so that each thread keeps 15 requests in flight.
         const int Wm4 = (W - 4) & ~3;
-        uint32_t* const gflat = &s.gray[0][0];
+        auto gray_word = [](uint32_t w0, uint32_t w1, uint32_t w2) {
+            const uint32_t t0 = gray_x2(w0), t1 = gray_x2(__funnelshift_r(w0, w1, 24));
+            const uint32_t t2 = gray_x2(__funnelshift_r(w1, w2, 16)), t3 = gray_x2(w2 >> 8);
+            return __byte_perm(__byte_perm(t0, t1, 0x0062), __byte_perm(t2, t3, 0x0062), 0x5410);
+        };
+        {
+            const uint8_t* pcol = img + 3 * min(max(x0 + 4 * lane, 0), Wm4);
+#pragma unroll 1
+            for (int j0 = 0; j0 < 10; j0 += 5) {
+                uint32_t w0[5], w1[5], w2[5];
 #pragma unroll
-        for (int b = 0; b < 2; ++b) {
-            constexpr int NB = 6;
-            uint32_t w0[NB], w1[NB], w2[NB];
-            int idx[NB];
+                for (int k = 0; k < 5; ++k) {
+                    const int ly = min(warp + 4 * (j0 + k), GH - 1);
+                    const int cy = min(max(y0 - 3 + ly, 0), H - 1);
+                    const uint32_t* p = reinterpret_cast<const uint32_t*>(pcol + (size_t)cy * stride);
+                    w0[k] = __ldg(p); w1[k] = __ldg(p + 1); w2[k] = __ldg(p + 2);
+                }
 #pragma unroll
-            for (int k = 0; k < NB; ++k) {
-                const int lyc = min(ly, GH - 1);
-                const int cy = min(max(y0 - 3 + lyc, 0), H - 1), cx = min(max(x0 - 4 + 4 * lw, 0), Wm4);
-                const uint32_t* p = reinterpret_cast<const uint32_t*>(img + (size_t)cy * stride + 3 * cx);
-                w0[k] = __ldg(p); w1[k] = __ldg(p + 1); w2[k] = __ldg(p + 2);
-                idx[k] = ly < GH ? lyc * GWW + lw : -1;
-                lw += NT % GWW; ly += NT / GWW;
-                if (lw >= GWW) { lw -= GWW; ++ly; }
-            }
-#pragma unroll
-            for (int k = 0; k < NB; ++k) {
-                const uint32_t t0 = gray_x2(w0[k]), t1 = gray_x2(__funnelshift_r(w0[k], w1[k], 24));
-                const uint32_t t2 = gray_x2(__funnelshift_r(w1[k], w2[k], 16)), t3 = gray_x2(w2[k] >> 8);
-                if (idx[k] >= 0)
-                    gflat[idx[k]] = __byte_perm(__byte_perm(t0, t1, 0x0062), __byte_perm(t2, t3, 0x0062), 0x5410);
+                for (int k = 0; k < 5; ++k) {
+                    const int ly = warp + 4 * (j0 + k);
+                    if (ly < GH) s.gray[ly][1 + lane] = gray_word(w0[k], w1[k], w2[k]);
+                }
             }
         }
-        static_assert(2 * 6 * NT >= GH * GWW, "two batches must cover the gray tile");
+        if (tid < 2 * GH) {  // halo words 0 and GWW-1
+            const int ly = tid >> 1, lw = (tid & 1) ? GWW - 1 : 0;
+            const int cy = min(max(y0 - 3 + ly, 0), H - 1), cx = min(max(x0 - 4 + 4 * lw, 0), Wm4);
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(img + (size_t)cy * stride + 3 * cx);
+            s.gray[ly][lw] = gray_word(__ldg(p), __ldg(p + 1), __ldg(p + 2));
+        }
     } else {
         for (int i = tid; i < GH * GWW; i += NT) {
             const int ly = i / GWW, lw = i - ly * GWW;
@@ -268,7 +273,7 @@ k_edge_candidates(const uint8_t* __restrict__ bgr, int W, int H, int stride, siz
         uint32_t ha[4], hb[4], hc[4];
         hrow_blur(s.gray[r0][lw - 1], s.gray[r0][lw], s.gray[r0][lw + 1], ha);
         hrow_blur(s.gray[r0 + 1][lw - 1], s.gray[r0 + 1][lw], s.gray[r0 + 1][lw + 1], hb);
-#pragma unroll
+#pragma unroll 3
         for (int r = 0; r < RPW; ++r) {
             const int gr = r0 + r + 2;
             hrow_blur(s.gray[gr][lw - 1], s.gray[gr][lw], s.gray[gr][lw + 1], hc);
