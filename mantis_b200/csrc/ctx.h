@@ -37,6 +37,8 @@ struct mantis_ctx {
     DevBuf hough_trig, hough_count, hough_peaks, hough_lines;  // line-voting stage (hough.cu)
     DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts
     int n_map = 0, n_green = 0, n_shift = 0;
+    int map_planar = 0;                      // every map point has z == 0 (the reference's floor grid)
+    DevBuf d_atan;                           // (i pi/256, tan(i pi/256)) table of the fast fp64 atan (search.cu)
     Tf rotz;                                 // +90 degrees about z
     DevBuf stage_in, stage_in2, stage_out0, stage_out1;  // device staging for MANTIS_MEM_HOST callers
     cudaStream_t copy_stream = nullptr;       // H2D of the next chunk while the current one computes

@@ -68,6 +68,16 @@ int ctx_init_tables(mantis_ctx* c)
     c->n_shift = (int)(sh.size() / 2);
     if ((rc = upload(c, c->d_shifts, sh.data(), sizeof(double) * sh.size()))) return rc;
 
+    {   // table of the fast atan in search.cu, rounded from long double
+        std::vector<double> tab(2 * 128);
+        const long double step = 3.14159265358979323846264338327950288L / 256.0L;
+        for (int i = 0; i < 128; ++i) {
+            tab[2 * i] = (double)(step * i);
+            tab[2 * i + 1] = (double)tanl(step * i);
+        }
+        if ((rc = upload(c, c->d_atan, tab.data(), sizeof(double) * tab.size()))) return rc;
+    }
+
     std::vector<double> xyz;
     int nw, nr, ng;
     default_map(c->cfg.grid_spacing, xyz, nw, nr, ng);
@@ -84,6 +94,9 @@ extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int
     if (rc) return rc;
     c->n_map = n;
     c->n_green = n_green;
+    c->map_planar = 1;
+    for (int i = 0; i < n; ++i)
+        if (xyz[3 * i + 2] != 0.0) c->map_planar = 0;
     return MANTIS_OK;
 }
 

@@ -31,12 +31,73 @@ struct Img {
     int W, H, WW, stride;
 };
 
+// ---- fp64 building blocks that stay on the DFMA pipe --------------------------------------------
+// The projection is issue-bound on fp64, and most of its instructions were the library division,
+// sqrt and atan.  These replacements seed from the fp32 special-function unit and finish with
+// Newton steps in fp64 (relative error a few 1e-16, i.e. the same last-bit neighbourhood as the
+// library routines); atan uses a 128-entry table of (theta_i, tan theta_i) and the addition formula,
+// so only a degree-7 odd polynomial on |x| <= 0.0123 remains.
+__device__ __forceinline__ double rcp_seed(double x)  // MUFU.RCP64H: relative error 2^-23
+{
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    return y;
+}
+__device__ __forceinline__ double rsqrt_seed(double x)  // MUFU.RSQ64H: relative error 2^-22
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    return y;
+}
+__device__ __forceinline__ double fast_rcp(double z)  // z normal and finite
+{
+    double y = rcp_seed(z);
+    double e = fma(-z, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-z, y, 1.0);
+    return fma(y, e, y);
+}
+__device__ __forceinline__ double fast_rsqrt(double x)  // x normal and finite
+{
+    double r = rsqrt_seed(x);
+    double e = fma(-(x * r), r, 1.0);
+    r = fma(0.5 * r, e, r);
+    e = fma(-(x * r), r, 1.0);
+    return fma(0.5 * r, e, r);
+}
+constexpr int ATAN_N = 128;  // table step h = pi/256 over [0, pi/2)
+// atan(r) for r >= 0 with inv_r = 1/r.  The table index only has to land within one step of the
+// angle, so it comes from a 3-term fp32 estimate (|error| < 0.004 rad = 0.31 h).
+__device__ __forceinline__ double fast_atan_pos(double r, double inv_r, const double2* __restrict__ tab)
+{
+    const bool big = r > 1.0;
+    const float q = (float)(big ? inv_r : r);
+    float est = q * fmaf(0.273f, 1.0f - q, 0.78539816f);
+    if (big) est = 1.57079633f - est;
+    const int i = min(__float2int_rn(est * 81.48733086305041f), ATAN_N - 1);  // 256/pi
+    const double2 e = tab[i];
+    const double x = (r - e.y) * fast_rcp(fma(r, e.y, 1.0));
+    const double x2 = x * x;
+    const double p = fma(x2, fma(x2, fma(x2, -1.0 / 7.0, 0.2), -1.0 / 3.0), 1.0);
+    return fma(x, p, e.x);
+}
+
 // img.at<Vec3b>(Point(x, y)) with the reference's unchecked linear addressing over a tightly
 // packed image: pixel index y*W + x; anything outside the buffer reads black.
 __device__ __forceinline__ int pixel_err(const Img& im, int x, int y, bool use_mask, int d0, int d1, int d2)
 {
-    long long pix = (long long)y * im.W + x;
     int b = 0, g = 0, r = 0;
+    if ((unsigned)x < (unsigned)im.W && (unsigned)y < (unsigned)im.H) {  // the common case
+        bool keep = true;
+        if (use_mask) keep = (__ldg(im.mask + (size_t)y * im.WW + (x >> 5)) >> (x & 31)) & 1u;
+        if (keep) {
+            const uint8_t* p = im.bgr + (size_t)y * im.stride + 3 * x;
+            b = __ldg(p); g = __ldg(p + 1); r = __ldg(p + 2);
+        }
+        int db = b - d0, dg = g - d1, dr = r - d2;
+        return db * db + dg * dg + dr * dr;
+    }
+    long long pix = (long long)y * im.W + x;
     if (pix >= 0 && pix < (long long)im.W * im.H) {
         int yy = y, xx = x;
         if ((unsigned)x >= (unsigned)im.W) { yy = (int)(pix / im.W); xx = (int)(pix - (long long)yy * im.W); }
@@ -51,14 +112,53 @@ __device__ __forceinline__ int pixel_err(const Img& im, int x, int y, bool use_m
     return db * db + dg * dg + dr * dr;
 }
 
-// Hypothesis::projectPoint + distortPixel + inFrame
-__device__ __forceinline__ bool project(const Tf& c2w, const pm::Camera& cam, const double* p, int W, int H, double& u,
-                                        double& v)
+// Hypothesis::projectPoint + distortPixel (Kannala-Brandt, Mantis3Types.h:88-136) + inFrame
+// (HypothesisEvaluation.h:388-398).  Same formulae as pm::fisheye_distort, with the fast fp64 blocks.
+struct CamK {
+    double fx, fy, cx, cy, D0, D1, D2, D3;
+    bool has_dist;
+};
+struct PoseXY {  // the part of a camera<-world transform that a floor-plane point needs, plus where the rest lives
+    double rx[3], ry[3], t[3];
+    const Tf* full;
+};
+__device__ __forceinline__ PoseXY load_pose(const Tf& c2w)
+{
+    PoseXY p;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { p.rx[i] = c2w.R[i * 3]; p.ry[i] = c2w.R[i * 3 + 1]; p.t[i] = c2w.t[i]; }
+    p.full = &c2w;
+    return p;
+}
+__device__ __forceinline__ bool project(const PoseXY& P, const CamK& cam, double px, double py, double pz, bool planar,
+                                        const double2* __restrict__ atan_tab, int W, int H, double& u, double& v)
 {
     double c[3];
-    for (int i = 0; i < 3; ++i) c[i] = (c2w.R[i * 3] * p[0] + c2w.R[i * 3 + 1] * p[1] + c2w.R[i * 3 + 2] * p[2]) + c2w.t[i];
-    if (!(c[2] > 0)) return false;
-    pm::fisheye_distort(cam, c[0] / c[2], c[1] / c[2], u, v);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        double acc = fma(P.rx[i], px, fma(P.ry[i], py, P.t[i]));
+        if (!planar) acc = fma(P.full->R[i * 3 + 2], pz, acc);  // the map is the floor plane: z = 0 adds nothing
+        c[i] = acc;
+    }
+    if (!(c[2] > 1e-300)) return false;  // behind the camera (the reference's z > 0), or no usable reciprocal
+    const double iz = fast_rcp(c[2]);
+    const double x = c[0] * iz, y = c[1] * iz;
+    const double r2 = fma(x, x, y * y);
+    double cdist = 1;
+    if (r2 > 1e-16 && r2 < 1e300) {  // r > 1e-8
+        const double inv_r = fast_rsqrt(r2), r = r2 * inv_r;
+        const double theta = fast_atan_pos(r, inv_r, atan_tab);
+        double theta_d = theta;
+        if (cam.has_dist) {
+            const double t2 = theta * theta;
+            theta_d = theta * fma(t2, fma(t2, fma(t2, fma(t2, cam.D3, cam.D2), cam.D1), cam.D0), 1.0);
+        }
+        cdist = theta_d * inv_r;
+    } else if (!(r2 <= 1e-16)) {
+        return false;  // overflow / NaN: the reference's atan(inf)/inf gives NaN pixel coordinates, never in frame
+    }
+    u = fma(x * cdist, cam.fx, cam.cx);
+    v = fma(y * cdist, cam.fy, cam.cy);
     return (u < W && v < H && u >= 0 && v > 0);
 }
 
@@ -70,7 +170,8 @@ struct SearchArgs {
     const FrameQuads* quads;
     const Hyp* hyps; const short* sel; const FramePose* info;
     const double* map;  // xyz, white | red | green
-    int n_map, n_green_off, n_green;
+    int n_map, n_green_off, n_green, map_planar;
+    const double2* atan_tab;  // (i pi/256, tan(i pi/256)), i < 128
     const Tf* rand_tf;  // [iterations * particles]
     const double* shifts;  // [n_shift][2]
     int n_shift, iterations, particles;
@@ -78,49 +179,58 @@ struct SearchArgs {
     double projection_bias, color_bias;
     mantis_result* out;
     mantis_frame_trace* trace;  // may be null
+    long long* dbg;             // tuning aid: clock64 per phase (null = off)
 };
 
 struct Shared {
-    double map[MAX_MAP * 3];
+    double map_x[MAX_MAP], map_y[MAX_MAP], map_z[MAX_MAP];
+    double2 atan_tab[ATAN_N];
     unsigned long long sum[1024];
     int cnt[1024];
     double err[1024];
     Tf cand_w2c[96], cand_c2w[96];
     Hyp best;
-    double green_val[80 * 40];
-    unsigned char green_ok[80 * 40];
+    unsigned int green_acc[80 * 40];  // integer colour error summed over the 10x10 window
+    int green_xy[80 * 40];            // cvRound(u) | cvRound(v) << 16 of the projected point, -1 if not in frame
+    unsigned char green_half[80 * 40];  // u or v exactly on a .5: per-pixel rounding differs from a shifted window
     double hyp_err[96];
     short top20[20];
 };
 
-// score `nh` hypotheses (c2w via the accessor) against all map points on the masked image
+// score `nh` hypotheses (c2w via the accessor) against all map points on the masked image.
+// The (hypothesis, 32-point chunk) tasks are cut into one contiguous range per warp, so a warp
+// reduces and publishes once per hypothesis it touches instead of once per chunk.
 template <class GetC2W>
-__device__ void score_white(Shared& s, const Img& im, const pm::Camera& cam, int n_map, int nh, double bias, GetC2W get)
+__device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map, bool planar, int nh, double bias,
+                            GetC2W get)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < nh; i += SNT) { s.sum[i] = 0ull; s.cnt[i] = 0; }
     __syncthreads();
     const int chunks = (n_map + 31) >> 5;
-    for (int task = warp; task < nh * chunks; task += NWARP) {
-        const int h = task / chunks, ch = task - h * chunks;
-        const Tf& c2w = get(h);
+    const int total = nh * chunks, per = (total + NWARP - 1) / NWARP;
+    const int t_begin = min(warp * per, total), t_end = min(t_begin + per, total);
+    int h = t_begin / chunks, ch = t_begin - h * chunks;
+    int e_acc = 0, ok_acc = 0;
+    PoseXY c2w;
+    if (t_begin < t_end) c2w = load_pose(get(h));
+    for (int t = t_begin; t < t_end; ++t) {
         const int pi = ch * 32 + lane;
-        int e = 0, ok = 0;
         if (pi < n_map) {
             double u, v;
-            if (project(c2w, cam, &s.map[3 * pi], im.W, im.H, u, v)) {
-                ok = 1;
-                e = pixel_err(im, __double2int_rn(u), __double2int_rn(v), true, 255, 255, 255);
+            if (project(c2w, cam, s.map_x[pi], s.map_y[pi], planar ? 0.0 : s.map_z[pi], planar, s.atan_tab, im.W, im.H, u, v)) {
+                ++ok_acc;
+                e_acc += pixel_err(im, __double2int_rn(u), __double2int_rn(v), true, 255, 255, 255);
             }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            e += __shfl_xor_sync(0xffffffffu, e, o);
-            ok += __shfl_xor_sync(0xffffffffu, ok, o);
-        }
-        if (lane == 0 && ok) {
-            atomicAdd(&s.sum[h], (unsigned long long)e);
-            atomicAdd(&s.cnt[h], ok);
+        if (++ch == chunks || t + 1 == t_end) {
+            const int e = __reduce_add_sync(0xffffffffu, e_acc), ok = __reduce_add_sync(0xffffffffu, ok_acc);
+            if (lane == 0 && ok) {
+                atomicAdd(&s.sum[h], (unsigned long long)e);
+                atomicAdd(&s.cnt[h], ok);
+            }
+            e_acc = 0; ok_acc = 0;
+            if (ch == chunks) { ch = 0; ++h; if (t + 1 < t_end) c2w = load_pose(get(h)); }
         }
     }
     __syncthreads();
@@ -162,14 +272,28 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     im.bgr = a.bgr + (size_t)frame * a.pitch;
     im.mask = a.mask_bits + (size_t)frame * a.H * a.WW;
     im.W = a.W; im.H = a.H; im.WW = a.WW; im.stride = a.stride;
-    const pm::Camera cam = a.cams[frame];
+    CamK cam;
+    {
+        const pm::Camera c0 = a.cams[frame];
+        cam.fx = c0.fx; cam.fy = c0.fy; cam.cx = c0.cx; cam.cy = c0.cy;
+        cam.D0 = c0.D[0]; cam.D1 = c0.D[1]; cam.D2 = c0.D[2]; cam.D3 = c0.D[3];
+        cam.has_dist = c0.D[0] != 0 || c0.D[1] != 0 || c0.D[2] != 0 || c0.D[3] != 0;
+    }
+    const bool planar = a.map_planar != 0;
     const Hyp* hyps = a.hyps + (size_t)frame * MANTIS_MAX_HYPS;
     const short* sel = a.sel + (size_t)frame * MANTIS_MAX_HYPS;
-    for (int i = tid; i < a.n_map * 3; i += SNT) s.map[i] = a.map[i];
+    for (int i = tid; i < a.n_map; i += SNT) {
+        s.map_x[i] = a.map[3 * i]; s.map_y[i] = a.map[3 * i + 1]; s.map_z[i] = a.map[3 * i + 2];
+    }
+    for (int i = tid; i < ATAN_N; i += SNT) s.atan_tab[i] = a.atan_tab[i];
     __syncthreads();
+    long long tk = clock64();
+    auto tick = [&](int slot) {
+        if (a.dbg && tid == 0) { long long t = clock64(); atomicAdd((unsigned long long*)&a.dbg[slot], (unsigned long long)(t - tk)); tk = t; }
+    };
 
     // (6) evaluateHypotheses on the kept cluster, (7) best 1
-    score_white(s, im, cam, a.n_map, n_sel, a.projection_bias, [&](int h) -> const Tf& { return hyps[sel[h]].c2w; });
+    score_white(s, im, cam, a.n_map, planar, n_sel, a.projection_bias, [&](int h) -> const Tf& { return hyps[sel[h]].c2w; });
     if (tid == 0) {
         int bi = 0;  // stable descending sort, last element: minimal error, highest index among ties
         for (int i = 1; i < n_sel; ++i)
@@ -180,6 +304,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     }
     __syncthreads();
 
+    tick(0);
     // (8) optimizeHypothesisWithParticleFilter
     for (int it = 0; it < a.iterations; ++it) {
         if (tid < a.particles) {
@@ -187,7 +312,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
             pm::tf_inv(s.cand_w2c[tid], s.cand_c2w[tid]);
         }
         __syncthreads();
-        score_white(s, im, cam, a.n_map, a.particles, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
+        score_white(s, im, cam, a.n_map, planar, a.particles, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
         if (tid == 0) {
             int bp = -1;
             double be = s.best.error;
@@ -207,6 +332,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
         for (int k = 0; k < 3; ++k) tr->optimized_w2c[9 + k] = s.best.w2c.t[k];
     }
 
+    tick(1);
     // (9) the 81 cell shifts, (10) evaluate
     const int ns = a.n_shift;
     if (tid < ns) {
@@ -218,7 +344,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
         pm::tf_inv(w, s.cand_c2w[tid]);
     }
     __syncthreads();
-    score_white(s, im, cam, a.n_map, ns, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
+    score_white(s, im, cam, a.n_map, planar, ns, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
     if (tr)
         for (int i = tid; i < ns && i < 81; i += SNT) tr->shift_err[i] = s.err[i];
     // (11) best 20: position in a stable descending sort; keep the last 20
@@ -231,6 +357,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     }
     __syncthreads();
 
+    tick(2);
     // (12) determineBestYaw on the original image: 4 rotations x `keep` hypotheses x green points
     // rotated copies: slot r*keep + k; reuse cand arrays beyond the shifts' slots is unsafe, so
     // stage the kept shifts first
@@ -245,27 +372,52 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     }
     __syncthreads();
     const int ng = a.n_green, nrot = 4 * keep;
+    // (a) project every green point of every rotated hypothesis once
     for (int item = tid; item < nrot * ng; item += SNT) {
-        const int h = item / ng, gi = item - h * ng;
+        const int h = item / ng, gi = item - h * ng, mi = a.n_green_off + gi;
         double u, v;
-        bool ok = project(s_rot_c2w[h], cam, &s.map[3 * (a.n_green_off + gi)], im.W, im.H, u, v);
-        double e = 0;
-        if (ok) {
+        const bool ok = project(load_pose(s_rot_c2w[h]), cam, s.map_x[mi], s.map_y[mi], s.map_z[mi], planar, s.atan_tab, im.W, im.H, u, v);
+        const int slot = h * 40 + gi;
+        s.green_acc[slot] = 0;
+        s.green_xy[slot] = ok ? ((__double2int_rn(u) & 0xffff) | (__double2int_rn(v) << 16)) : -1;
+        // cvRound(u + dx) == cvRound(u) + dx unless u sits exactly on a half (round-half-even)
+        s.green_half[slot] = ok && (u - floor(u) == 0.5 || v - floor(v) == 0.5);
+        if (ok && s.green_half[slot]) {
             long long acc = 0;
             for (int dx = -5; dx < 5; ++dx)
                 for (int dy = -5; dy < 5; ++dy)
                     acc += pixel_err(im, __double2int_rn(u + (double)dx), __double2int_rn(v + (double)dy), false, 50, 255, 85);
-            e = (double)acc / 100.0;
+            s.green_acc[slot] = (unsigned int)acc;
         }
-        s.green_val[h * 40 + gi] = e;
-        s.green_ok[h * 40 + gi] = ok;
     }
+    __syncthreads();
+    // (b) the 10x10 windows, one window column per work item; integer sums commute
+    for (int item = tid; item < nrot * ng * 10; item += SNT) {
+        const int slot_i = item / 10, k = item - slot_i * 10;
+        const int h = slot_i / ng, gi = slot_i - h * ng, slot = h * 40 + gi;
+        const int xy = s.green_xy[slot];
+        if (xy < 0 || s.green_half[slot]) continue;
+        const int x = (int)(short)(xy & 0xffff) + (k - 5), y0 = (xy >> 16) - 5;
+        unsigned int acc = 0;
+        if ((unsigned)x < (unsigned)im.W && y0 >= 0 && y0 + 9 < im.H) {
+            const uint8_t* p = im.bgr + (size_t)y0 * im.stride + 3 * x;
+#pragma unroll
+            for (int dy = 0; dy < 10; ++dy, p += im.stride) {
+                const int db = (int)__ldg(p) - 50, dg = (int)__ldg(p + 1) - 255, dr = (int)__ldg(p + 2) - 85;
+                acc += (unsigned)(db * db + dg * dg + dr * dr);
+            }
+        } else {
+            for (int dy = 0; dy < 10; ++dy) acc += (unsigned)pixel_err(im, x, y0 + dy, false, 50, 255, 85);
+        }
+        atomicAdd(&s.green_acc[slot], acc);
+    }
+    tick(3);
     __syncthreads();
     if (tid < nrot) {
         double err = 0;
         int n = 0;
         for (int gi = 0; gi < ng; ++gi)
-            if (s.green_ok[tid * 40 + gi]) { err += s.green_val[tid * 40 + gi]; ++n; }
+            if (s.green_xy[tid * 40 + gi] >= 0) { err += (double)s.green_acc[tid * 40 + gi] / 100.0; ++n; }
         s.hyp_err[tid] = n > 0 ? err / ((double)n * a.color_bias) : DBLMAX;
     }
     __syncthreads();
@@ -319,6 +471,8 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
     a.cams = d_cams; a.quads = d_quads; a.hyps = d_hyps; a.sel = d_sel; a.info = d_info;
     a.map = (const double*)c->d_map.p;
     a.n_map = c->n_map; a.n_green_off = c->n_map - c->n_green; a.n_green = c->n_green;
+    a.map_planar = c->map_planar;
+    a.atan_tab = (const double2*)c->d_atan.p;
     a.rand_tf = (const Tf*)c->d_rand.p;
     a.shifts = (const double*)c->d_shifts.p;
     a.n_shift = c->n_shift; a.iterations = c->cfg.iterations; a.particles = c->cfg.particles;
@@ -326,6 +480,7 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
     a.projection_bias = c->cfg.projection_bias;
     a.color_bias = c->cfg.color_projection_bias;
     a.out = d_out; a.trace = d_trace;
+    a.dbg = (long long*)c->dbg_clocks;
     const size_t smem = sizeof(Shared);
     MCHECK(c, cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_search<<<n, SNT, smem, c->stream>>>(a);
