@@ -89,9 +89,9 @@ __device__ __forceinline__ int pixel_err(const Img& im, int x, int y, bool use_m
     int b = 0, g = 0, r = 0;
     if ((unsigned)x < (unsigned)im.W && (unsigned)y < (unsigned)im.H) {  // the common case
         bool keep = true;
-        if (use_mask) keep = (__ldg(im.mask + (size_t)y * im.WW + (x >> 5)) >> (x & 31)) & 1u;
+        if (use_mask) keep = (__ldg(im.mask + (unsigned)(y * im.WW + (x >> 5))) >> (x & 31)) & 1u;
         if (keep) {
-            const uint8_t* p = im.bgr + (size_t)y * im.stride + 3 * x;
+            const uint8_t* p = im.bgr + (unsigned)(y * im.stride + 3 * x);
             b = __ldg(p); g = __ldg(p + 1); r = __ldg(p + 2);
         }
         int db = b - d0, dg = g - d1, dr = r - d2;
@@ -190,6 +190,7 @@ struct Shared {
     double err[1024];
     Tf cand_w2c[96], cand_c2w[96];
     Hyp best;
+    Img img;  // per-frame image descriptor: kept here so that the base pointers are one broadcast load away
     unsigned int green_acc[80 * 40];  // integer colour error summed over the 10x10 window
     int green_xy[80 * 40];            // cvRound(u) | cvRound(v) << 16 of the projected point, -1 if not in frame
     unsigned char green_half[80 * 40];  // u or v exactly on a .5: per-pixel rounding differs from a shifted window
@@ -268,10 +269,12 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     }
     if (fq->flags || fq->n_quads == 0 || n_sel == 0) return;
 
-    Img im;
-    im.bgr = a.bgr + (size_t)frame * a.pitch;
-    im.mask = a.mask_bits + (size_t)frame * a.H * a.WW;
-    im.W = a.W; im.H = a.H; im.WW = a.WW; im.stride = a.stride;
+    if (tid == 0) {
+        s.img.bgr = a.bgr + (size_t)frame * a.pitch;
+        s.img.mask = a.mask_bits + (size_t)frame * a.H * a.WW;
+        s.img.W = a.W; s.img.H = a.H; s.img.WW = a.WW; s.img.stride = a.stride;
+    }
+    const Img& im = s.img;  // published by the barrier below
     CamK cam;
     {
         const pm::Camera c0 = a.cams[frame];
