@@ -171,6 +171,37 @@ int mantis_hough_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, in
                        size_t frame_pitch_bytes, const mantis_hough_params* prm, mantis_frame_lines* out, int mem);
 
 /*
+ * Gauss-Newton / Levenberg-Marquardt PnP, batched: the mantis2 generation's pose step
+ *   computeHypothesis -> cv::solvePnP(obj, img, K, noArray, rvec, tvec, useExtrinsicGuess, SOLVEPNP_ITERATIVE)
+ *                                                   include/legacy/mantis2/PoseEstimator.h:91-118
+ *   error = computeHypothesisQuadReprojectionError  :16-25   (sqrt of the summed squared pixel residuals)
+ * One pose per frame from m correspondences (pinhole K, no distortion, as the legacy call passes noArray).
+ *   obj_xyz   m*3 floats per frame (or one shared set when obj_shared != 0)
+ *   img_xy    m*2 floats per frame (pixels)
+ *   K         9 floats per frame, row-major (or one shared K when k_shared != 0)
+ *   guess_rt  optional: rvec(3) + tvec(3) doubles per frame = useExtrinsicGuess; NULL = planar (z = 0)
+ *             initialisation from a homography, as OpenCV does for planar objects
+ * The result is the minimiser of the reprojection error in the basin of the initial pose (OpenCV's LM
+ * converges to the same point; its iteration path is not reproduced).
+ */
+enum { MANTIS_PNP_BOTH_PLANAR = 1 };  /* params.flags: also refine the mirrored planar candidate, keep the better (cf. RPP.cpp:36-52) */
+enum { MANTIS_PNP_OK = 0, MANTIS_PNP_DEGENERATE = 1 };
+typedef struct mantis_pnp_params {
+    int32_t flags;
+    int32_t max_iters;  /* LM iterations per candidate; <= 0 means 50 */
+} mantis_pnp_params;
+typedef struct mantis_pnp_result {
+    double rvec[3];       /* Rodrigues vector, cv::Rodrigues' branch conventions */
+    double tvec[3];
+    double reproj_error;  /* computeHypothesisQuadReprojectionError */
+    int32_t passes;       /* evaluations of the normal equations */
+    int32_t status;
+} mantis_pnp_result;
+int mantis_pnp_batch(mantis_ctx* ctx, const float* obj_xyz, const float* img_xy, int n, int m, int obj_shared,
+                     const float* K, int k_shared, const double* guess_rt, const mantis_pnp_params* prm,
+                     mantis_pnp_result* out, int mem);
+
+/*
  * Whole-frame localization: everything quadDetection() does between receiving the image and
  * calling publishPose() (src/mantis3.cpp:68-135).
  */

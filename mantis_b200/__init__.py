@@ -17,6 +17,7 @@ from .binding import (  # noqa: F401
     FrameTrace,
     Result,
     MantisError,
+    PnpResult,
     build_library,
     library_path,
     load_library,

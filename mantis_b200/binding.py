@@ -108,6 +108,20 @@ class HoughParams(ctypes.Structure):
                 ("theta_tol", ctypes.c_double), ("pencil_tol", ctypes.c_double)]
 
 
+class PnpParams(ctypes.Structure):
+    _fields_ = [("flags", ctypes.c_int32), ("max_iters", ctypes.c_int32)]
+
+
+class PnpResult(ctypes.Structure):
+    """mantis_pnp_result."""
+
+    _fields_ = [("rvec", ctypes.c_double * 3), ("tvec", ctypes.c_double * 3), ("reproj_error", ctypes.c_double),
+                ("passes", ctypes.c_int32), ("status", ctypes.c_int32)]
+
+
+PNP_BOTH_PLANAR = 1
+
+
 def library_path():
     return os.path.join(_HERE, "libmantis_cuda.so")
 
@@ -153,6 +167,8 @@ def load_library():
                                        c.c_void_p, c.c_int]
     lib.mantis_hough_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
                                        c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_pnp_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p, c.c_int,
+                                     c.c_void_p, c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_set_map.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int]
     lib.mantis_localize_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_render_grid_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p,
@@ -281,6 +297,29 @@ class Context:
                                           ctypes.addressof(out), MEM_HOST)
         self._check(rc, "mantis_hough_batch")
         return out
+
+    # -- computeHypothesis(): solvePnP(ITERATIVE) + reprojection error, legacy/mantis2/PoseEstimator.h:16-25,91-118 --
+    def pnp(self, obj, img, K, guess=None, both_planar=False, max_iters=0):
+        """obj [n,m,3] or [m,3] (shared), img [n,m,2], K [3,3] (shared) or [n,3,3] -> (PnpResult * n)."""
+        img = np.ascontiguousarray(img, np.float32)
+        obj = np.ascontiguousarray(obj, np.float32)
+        K = np.ascontiguousarray(K, np.float32)
+        n, m, _ = img.shape
+        g = None if guess is None else np.ascontiguousarray(guess, np.float64).reshape(n, 6)
+        out = (PnpResult * n)()
+        prm = PnpParams(PNP_BOTH_PLANAR if both_planar else 0, int(max_iters))
+        rc = self._lib.mantis_pnp_batch(self._h, _ptr(obj), _ptr(img), n, m, int(obj.ndim == 2), _ptr(K), int(K.ndim == 2),
+                                        _ptr(g), ctypes.byref(prm), ctypes.addressof(out), MEM_HOST)
+        self._check(rc, "mantis_pnp_batch")
+        return out
+
+    def pnp_device(self, d_obj, d_img, n, m, d_K, d_out, obj_shared=False, k_shared=True, d_guess=None, both_planar=False,
+                   max_iters=0):
+        """Device-resident variant (integer device pointers); d_out receives n mantis_pnp_result records."""
+        prm = PnpParams(PNP_BOTH_PLANAR if both_planar else 0, int(max_iters))
+        rc = self._lib.mantis_pnp_batch(self._h, _ptr(d_obj), _ptr(d_img), n, m, int(obj_shared), _ptr(d_K), int(k_shared),
+                                        _ptr(d_guess), ctypes.byref(prm), _ptr(d_out), MEM_DEVICE)
+        self._check(rc, "mantis_pnp_batch")
 
     # -- quadDetection(), src/mantis3.cpp:68-135 --
     def set_map(self, white, red, green):

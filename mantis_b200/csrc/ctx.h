@@ -34,6 +34,7 @@ struct mantis_ctx {
     DevBuf quad_hyp, pose_offs;
     DevBuf cams, hyps, sel, pose_info, results, traces, mask_bits;  // localize scratch (per chunk)
     DevBuf render_poses;
+    DevBuf pnp_stage;                        // host-caller staging of mantis_pnp_batch
     DevBuf hough_trig, hough_count, hough_peaks, hough_lines;  // line-voting stage (hough.cu)
     DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts
     int n_map = 0, n_green = 0, n_shift = 0;

@@ -66,6 +66,12 @@ double mo_rng_gaussian(uint64_t* state, double sigma);
 int mo_rpp(const double* model3xn, const double* iprts3xn, int n, double* R9, double* t3, int* iters,
            double* obj_err, double* img_err);
 
+/* ---- Gauss-Newton / PnP in its mantis2 meaning: include/legacy/mantis2/PoseEstimator.h:16-25,91-118 ---- */
+void mo_rodrigues_exp(const double* w, double* R);
+void mo_rodrigues_log(const double* R, double* w);
+int mo_pnp_iterative(const float* obj, const float* img, int m, const float* K, const double* guess6, int flags,
+                     int max_iters, double* out9);
+
 /* ---- synthetic frame source (stands in for GridRenderer.cpp:211-353) ---- */
 void mo_render_grid(const double* R_w2c, const double* t_w2c, const float* K, const double* D, int w, int h,
                     double line_width, int floor_level, uint8_t* bgr);

@@ -355,3 +355,28 @@ def hough_intersections(clusters, w, h, pencil_tol=np.deg2rad(25.0), max_points=
                   ctypes.c_int, ctypes.c_void_p]
     m = f(ctypes.addressof(arr), n, w, h, float(pencil_tol), xy.ctypes.data, max_points, pen.ctypes.data)
     return xy[:m].copy(), pen[:n].copy()
+
+
+# ---- PnP (config 5; cv::solvePnP(ITERATIVE) semantics, see oracle/pnp.c) ----
+def pnp_iterative(obj, img, K, guess=None, both_planar=False, max_iters=50):
+    """obj [m,3], img [m,2] (converted to float32 as the C ABI takes them) -> dict(rvec, tvec, err, passes, ok)."""
+    obj = np.ascontiguousarray(obj, np.float32)
+    img = np.ascontiguousarray(img, np.float32)
+    Kf = np.ascontiguousarray(K, np.float32).reshape(-1)
+    g = None if guess is None else np.ascontiguousarray(guess, np.float64).reshape(6)
+    out = np.zeros(9, np.float64)
+    f = lib().mo_pnp_iterative
+    f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                  ctypes.c_int, ctypes.c_void_p]
+    ok = f(obj.ctypes.data, img.ctypes.data, len(obj), Kf.ctypes.data, None if g is None else g.ctypes.data,
+           1 if both_planar else 0, int(max_iters), out.ctypes.data)
+    return dict(rvec=out[:3].copy(), tvec=out[3:6].copy(), err=float(out[6]), passes=int(out[7]), ok=bool(ok))
+
+
+def rodrigues_exp(w):
+    R = np.zeros(9)
+    f = lib().mo_rodrigues_exp
+    f.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    w = np.ascontiguousarray(w, np.float64)
+    f(w.ctypes.data, R.ctypes.data)
+    return R.reshape(3, 3)
