@@ -94,17 +94,17 @@ int mantis_destroy(mantis_ctx* c)
 }
 
 // Tuning aid (not part of the public header): accumulated clock64 deltas of the quad kernel's phases.
-int mantis_debug_clocks(mantis_ctx* c, long long* out8)
+int mantis_debug_clocks(mantis_ctx* c, long long* out16)
 {
     if (!c) return MANTIS_ERR_INVALID;
     MCHECK(c, cudaSetDevice(c->device));
     if (!c->dbg_clocks) {
-        MCHECK(c, cudaMalloc(&c->dbg_clocks, 8 * sizeof(long long)));
-        MCHECK(c, cudaMemset(c->dbg_clocks, 0, 8 * sizeof(long long)));
+        MCHECK(c, cudaMalloc(&c->dbg_clocks, 16 * sizeof(long long)));
+        MCHECK(c, cudaMemset(c->dbg_clocks, 0, 16 * sizeof(long long)));
     }
-    if (out8) {
-        MCHECK(c, cudaMemcpy(out8, c->dbg_clocks, 8 * sizeof(long long), cudaMemcpyDeviceToHost));
-        MCHECK(c, cudaMemset(c->dbg_clocks, 0, 8 * sizeof(long long)));
+    if (out16) {
+        MCHECK(c, cudaMemcpy(out16, c->dbg_clocks, 16 * sizeof(long long), cudaMemcpyDeviceToHost));
+        MCHECK(c, cudaMemset(c->dbg_clocks, 0, 16 * sizeof(long long)));
     }
     return MANTIS_OK;
 }

@@ -21,7 +21,7 @@ struct mantis_ctx {
     char err[256] = {0};
 
     // optional per-stage timing (CUDA events on the context stream)
-    void* dbg_clocks = nullptr;  // device array of 8 long long, set by mantis_debug_clocks
+    void* dbg_clocks = nullptr;  // device array of 16 long long, set by mantis_debug_clocks
     bool profiling = false;
     cudaEvent_t ev[MANTIS_N_STAGES + 1] = {};
     double stage_ms[MANTIS_N_STAGES] = {};

@@ -11,8 +11,8 @@
 // cluster and halo rows are exchanged through distributed shared memory (DSMEM).
 //   closure : E <- strong;  repeat E <- weak & flood(E | dilate3x3(E)) until stable.  In-word
 //             horizontal runs are filled in O(1) with the carry trick ((M+S)^M)&M.
-//   3x3 max : out-of-image pixels never win == OR with 0 outside
-//   3x3 min : out-of-image pixels never win == AND with 1 outside
+//   k x (3x3 max) == (2k+1)^2 box OR with 0 outside the image, done as a row pass and a column pass
+//   k x (3x3 min) == the same on the complement (1 outside the image)
 #include <cooperative_groups.h>
 #include "ctx.h"
 
@@ -46,6 +46,7 @@ struct LinkArgs {
     uint8_t* morph_u8;
     uint8_t* mask_u8;
     int W, H, WW, HC;  // HC = rows per CTA
+    long long* dbg;    // tuning aid: clock64 per phase (null = off)
 };
 
 // Geometry of this CTA's band of rows.  Planes are stored as (HC+2) x WW words: local row 0
@@ -163,13 +164,59 @@ __device__ __forceinline__ uint32_t stencil(const uint32_t* s, const Band& b, in
     return o;
 }
 
-template <bool OR>
-__device__ void box3(const uint32_t* src, uint32_t* dst, const Band& b)
+// k iterations of the 3x3 dilation (erode = false) or erosion (erode = true) in two separable passes:
+// src -(rows: OR of shifts -k..k)-> tmp -(columns: OR of rows -k..k)-> src.  Erosion runs on the
+// complement (outside the image counts as 1, i.e. never wins the minimum).  One compact routine for every
+// morphological step of the kernel keeps the code inside the instruction cache.
+__device__ __noinline__ void morph_op(cg::cluster_group& cluster, uint32_t* src, uint32_t* tmp, const Band& b, int k,
+                                      bool erode, int CS)
 {
-    for (int i = threadIdx.x; i < b.nrows * b.WW; i += LNT) {
-        int lr = i / b.WW + 1, j = i - (lr - 1) * b.WW;
-        dst[lr * b.WW + j] = stencil<OR, true>(src, b, lr, j);
+    const int WW = b.WW, n = b.nrows * WW;
+    const uint32_t inv = erode ? 0xffffffffu : 0u;
+    // (row, word) of this thread's first item and the step of LNT items, so that the loops need no division
+    const int lr0 = threadIdx.x / WW + 1, j0 = threadIdx.x - (lr0 - 1) * WW, dlr = LNT / WW, dj = LNT - dlr * WW;
+    int lr = lr0, j = j0;
+    for (int i = threadIdx.x; i < n; i += LNT) {
+        const uint32_t* row = src + lr * WW;
+        uint32_t C = row[j] ^ inv, L = j > 0 ? row[j - 1] ^ inv : 0u, R = j + 1 < WW ? row[j + 1] ^ inv : 0u;
+        if (j == WW - 1) C &= b.last_mask;
+        if (j + 1 == WW - 1) R &= b.last_mask;
+        uint32_t acc = C;
+        for (int d = 1; d <= k; ++d) acc |= __funnelshift_l(L, C, d) | __funnelshift_r(C, R, d);
+        if (j == WW - 1) acc &= b.last_mask;
+        tmp[lr * WW + j] = acc;
+        lr += dlr; j += dj;
+        if (j >= WW) { j -= WW; ++lr; }
     }
+    if (CS > 1) cluster.sync(); else __syncthreads();
+    // column pass: rows of this CTA's band from local shared memory, rows of the neighbouring bands (only
+    // when the frame is split over a cluster) straight from their shared memory; rows outside the image add 0
+    const uint32_t* up = nullptr;
+    const uint32_t* down = nullptr;
+    int down_rows = 0;
+    if (CS > 1) {
+        if (b.rank > 0 && b.nrows > 0) up = cluster.map_shared_rank(tmp, b.rank - 1);
+        if (b.rank < b.last_rank) {
+            down = cluster.map_shared_rank(tmp, b.rank + 1);
+            down_rows = min(b.HC, b.H - (b.rank + 1) * b.HC);
+        }
+    }
+    lr = lr0; j = j0;
+    for (int i = threadIdx.x; i < n; i += LNT) {
+        const int lo = max(1, lr - k), hi = min(b.nrows, lr + k);
+        uint32_t acc = 0;
+        for (int r = lo; r <= hi; ++r) acc |= tmp[r * WW + j];
+        if (up)
+            for (int r = lr - k; r < 1; ++r) acc |= up[(b.HC + r) * WW + j];
+        if (down)
+            for (int r = b.nrows + 1; r <= min(lr + k, b.nrows + down_rows); ++r) acc |= down[(r - b.nrows) * WW + j];
+        acc ^= inv;
+        if (j == WW - 1) acc &= b.last_mask;
+        src[lr * WW + j] = acc;
+        lr += dlr; j += dj;
+        if (j >= WW) { j -= WW; ++lr; }
+    }
+    if (CS > 1) cluster.sync(); else __syncthreads();
 }
 
 __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
@@ -206,6 +253,11 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
     if (threadIdx.x < 16) (&s_flags[0][0])[threadIdx.x] = 0;
     __syncthreads();
 
+    long long tk = clock64();
+    auto tick = [&](int slot) {
+        if (a.dbg && threadIdx.x == 0) { long long t = clock64(); atomicAdd((unsigned long long*)&a.dbg[slot], (unsigned long long)(t - tk)); tk = t; }
+    };
+    tick(4);
     // ---- hysteresis closure (in place, monotone: racing reads are benign) ----
     int parity = 0;
     for (;;) {
@@ -243,26 +295,25 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
         if (!any) break;
     }
 
+    tick(5);
     if (a.canny_u8) store_u8(B, b, a.canny_u8 + (size_t)frame * b.W * b.H);
     if (a.canny_bits) store_bits(B, b, a.canny_bits + plane);
+    tick(8);
 
     const bool want_morph = a.morph_u8 || a.morph_bits;
     const bool want_mask = a.mask_u8 || a.mask_bits;
     if (!want_morph && !want_mask) return;  // uniform across the cluster
 
     if (want_morph) {
-        // dilate x2, erode x1: B -> A -> B -> A (halo rows of B are current after the closure)
-        __syncthreads();
-        box3<true>(B, A, b);
-        refresh_halo(cluster, A, b, CS);
-        box3<true>(A, B, b);
-        refresh_halo(cluster, B, b, CS);
-        box3<false>(B, A, b);
-        __syncthreads();
-        if (a.morph_u8) store_u8(A, b, a.morph_u8 + (size_t)frame * b.W * b.H);
-        if (a.morph_bits) store_bits(A, b, a.morph_bits + plane);
+        // dilate x2, erode x1 on the closure result (B -> A -> B)
+        if (CS > 1) cluster.sync(); else __syncthreads();
+        morph_op(cluster, B, A, b, 2, false, CS);
+        morph_op(cluster, B, A, b, 1, true, CS);
+        tick(9);
+        if (a.morph_u8) store_u8(B, b, a.morph_u8 + (size_t)frame * b.W * b.H);
+        if (a.morph_bits) store_bits(B, b, a.morph_bits + plane);
     }
-
+    tick(6);
     if (want_mask) {
         // the closure result was overwritten by the ping-pong: reload it (L2-resident) into B
         if (CS > 1) cluster.sync();  // neighbours may still be pulling from B / A
@@ -289,23 +340,18 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
             uint32_t interior = t & u & d & ((t << 1) | (cl >> 31)) & ((t >> 1) | (cr << 31));
             B[lr * WW + j] |= (t & ~interior);
         }
-        // closes of 3, 4, 5 iterations then erode 3 (each k-iteration op == k passes of 3x3)
-        uint32_t* src = B;
-        uint32_t* dst = A;
-        auto pass = [&](bool is_or) {
-            refresh_halo(cluster, src, b, CS);
-            if (is_or) box3<true>(src, dst, b); else box3<false>(src, dst, b);
-            uint32_t* t = src; src = dst; dst = t;
-        };
-        for (int it = 0; it < 3; ++it) {
-            for (int k = 0; k < 3 + it; ++k) pass(true);
-            for (int k = 0; k < 3 + it; ++k) pass(false);
-        }
-        for (int k = 0; k < 3; ++k) pass(false);
-        __syncthreads();
-        if (a.mask_u8) store_u8(src, b, a.mask_u8 + (size_t)frame * b.W * b.H);
-        if (a.mask_bits) store_bits(src, b, a.mask_bits + plane);
+        // closes of 3, 4, 5 iterations then erode 3: dilate 3, erode 3, dilate 4, erode 4, dilate 5, erode 5 + 3
+        if (CS > 1) cluster.sync(); else __syncthreads();
+        morph_op(cluster, B, A, b, 3, false, CS);
+        morph_op(cluster, B, A, b, 3, true, CS);
+        morph_op(cluster, B, A, b, 4, false, CS);
+        morph_op(cluster, B, A, b, 4, true, CS);
+        morph_op(cluster, B, A, b, 5, false, CS);
+        morph_op(cluster, B, A, b, 8, true, CS);
+        if (a.mask_u8) store_u8(B, b, a.mask_u8 + (size_t)frame * b.W * b.H);
+        if (a.mask_bits) store_bits(B, b, a.mask_bits + plane);
     }
+    tick(7);
     // keep this CTA's shared memory alive until every neighbour has finished pulling from it
     if (CS > 1) cluster.sync();
 }
@@ -338,6 +384,7 @@ int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_st
     a.canny_u8 = out.canny_u8; a.morph_u8 = out.morph_u8; a.mask_u8 = out.mask_u8;
     a.W = w; a.H = h; a.WW = WW; a.HC = (h + cs - 1) / cs;
     if ((a.mask_bits || a.mask_u8) && !a.canny_bits) return MANTIS_ERR_INVALID;
+    a.dbg = (long long*)c->dbg_clocks;
     smem = (size_t)2 * (a.HC + 2) * WW * sizeof(uint32_t);
 
     MCHECK(c, cudaFuncSetAttribute(k_edge_link, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

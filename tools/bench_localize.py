@@ -28,7 +28,7 @@ def main():
           np.mean([r.n_hyps for r in res]), "mean scored", np.mean([r.n_particles for r in res]))
     ctx.set_profiling(True)
     import ctypes
-    clk = (ctypes.c_longlong * 8)()
+    clk = (ctypes.c_longlong * 16)()
     ctx._lib.mantis_debug_clocks(ctx._h, None)
     ts = []
     for _ in range(iters):
@@ -38,7 +38,9 @@ def main():
     ms = ctx.stage_ms()
     ctx._lib.mantis_debug_clocks(ctx._h, clk)
     tot = sum(clk) or 1
-    print('quad kernel phase shares (cand, probe, sort, emit, approx+parent, order, dedupe):', [round(v / tot, 3) for v in clk][:7], 'cycles/frame', tot / (N * iters))
+    per = [round(v / (N * iters)) for v in clk]
+    print('search kernel cycles/frame (first score, refinement, shifts, yaw windows):', per[:4])
+    print('edge-link kernel cycles/frame (load, hysteresis, canny store, 3 morph passes, morph store, mask chain):', [per[4], per[5], per[8], per[9], per[6], per[7]])
     print({k: round(v / iters, 2) for k, v in ms.items()})
     print(f"{W}x{H} x{N}: best {min(ts)*1e3:.1f} ms  -> {N/min(ts):.0f} frames/s")
 
