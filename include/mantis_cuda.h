@@ -253,6 +253,38 @@ int mantis_localize_batch(mantis_ctx* ctx, const mantis_frame* frames, int n, ma
                           mantis_frame_trace* trace, int mem);
 
 /*
+ * The 2016 generation's particle weight, batched over particles x frames:
+ *   MonteCarlo::computeCameraError / project2d / computeWeight   include/legacy/mantis/MonteCarlo.cpp:169-241
+ * Pinhole projection of the context's map (white, red, green) by every world->camera transform onto an
+ * UNDISTORTED image; colour SSE against WHITE (255,255,255), RED (113,48,32), GREEN (50,100,37)
+ * (MonteCarlo.h:53-55); fewer than 10 projected points -> 1e17 / count, as written.
+ *   K         9 floats per frame (CameraInfo.K narrowed to CV_32F, MonteCarlo.cpp:148-161)
+ *   w2c       per frame, per particle: R row-major (9) + t (3) doubles -- w2c1 of computeWeight (:234-236)
+ *   weights   n * n_particles doubles
+ */
+int mantis_particle_weights_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                                  size_t frame_pitch_bytes, const float* K, const double* w2c, int n_particles,
+                                  double* weights, int mem);
+
+/* cv::fisheye::undistortImage(img, out, K, D, Knew = K) as parseRequest calls it (MonteCarlo.cpp:284): one
+ * camera (upper-triangular K, 4 fisheye coefficients) for all n frames; out is n tightly packed BGR frames. */
+int mantis_undistort_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                           size_t frame_pitch_bytes, const float* K, const double* D, uint8_t* out, int mem);
+
+/*
+ * Temporal yaw filter, one 360-bin plane per camera stream: MarkovModel of
+ * include/mantis3/Markov.cpp.  planes: n_streams x 360 doubles, updated in place.
+ *   MANTIS_MARKOV_INIT      a = yaw (rad) of the first hypothesis' W2C: MarkovModel(Hypothesis)      :14-26
+ *   MANTIS_MARKOV_CONVOLVE  a = dTheta (rad), b = dt (s): convolve()                                    :227-258
+ *   MANTIS_MARKOV_SENSE     a = yaw (rad) of the accepted hypothesis: senseFusion(Hypothesis)           :164-205
+ * mantis_markov_update_errors scales hypothesis errors by 1/p[yaw bin] of their stream: updateHypothesis() :207-220
+ */
+enum { MANTIS_MARKOV_INIT = 0, MANTIS_MARKOV_CONVOLVE = 1, MANTIS_MARKOV_SENSE = 2 };
+int mantis_markov_batch(mantis_ctx* ctx, double* planes, int n_streams, int op, const double* a, const double* b, int mem);
+int mantis_markov_update_errors(mantis_ctx* ctx, const double* planes, int n_streams, const int* stream_of,
+                                const double* yaw, double* err, int n_hyps, int mem);
+
+/*
  * Synthetic frame source on the device: the floor grid of params/map.yaml ray-cast through the
  * fisheye model for n camera poses (stands in for GridRenderer::renderGrid,
  * include/mantis3/GridRenderer.cpp:292-353, whose OpenGL path cannot run here).

@@ -169,6 +169,13 @@ def load_library():
                                        c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_pnp_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p, c.c_int,
                                      c.c_void_p, c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_particle_weights_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
+                                                  c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_int]
+    lib.mantis_undistort_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
+                                           c.c_void_p, c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_markov_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_markov_update_errors.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p,
+                                                c.c_int, c.c_int]
     lib.mantis_set_map.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int]
     lib.mantis_localize_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_render_grid_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p,
@@ -320,6 +327,57 @@ class Context:
         rc = self._lib.mantis_pnp_batch(self._h, _ptr(d_obj), _ptr(d_img), n, m, int(obj_shared), _ptr(d_K), int(k_shared),
                                         _ptr(d_guess), ctypes.byref(prm), _ptr(d_out), MEM_DEVICE)
         self._check(rc, "mantis_pnp_batch")
+
+    # -- 2016 generation: computeCameraError / undistortImage, legacy/mantis/MonteCarlo.cpp:169-241,284 --
+    def particle_weights(self, bgr, K, w2c):
+        """bgr [n,H,W,3] (undistorted), K [n,3,3] or [3,3], w2c [n,P,12] -> weights [n,P]."""
+        bgr = np.ascontiguousarray(bgr, np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, _ = bgr.shape
+        K = np.ascontiguousarray(K, np.float32)
+        if K.ndim == 2:
+            K = np.repeat(K[None], n, 0)
+        w2c = np.ascontiguousarray(w2c, np.float64).reshape(n, -1, 12)
+        out = np.zeros((n, w2c.shape[1]), np.float64)
+        rc = self._lib.mantis_particle_weights_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, _ptr(K), _ptr(w2c),
+                                                     w2c.shape[1], _ptr(out), MEM_HOST)
+        self._check(rc, "mantis_particle_weights_batch")
+        return out
+
+    def undistort(self, bgr, K, D):
+        bgr = np.ascontiguousarray(bgr, np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, _ = bgr.shape
+        Kf, Dd = np.ascontiguousarray(K, np.float32), np.ascontiguousarray(D, np.float64)
+        out = np.zeros_like(bgr)
+        rc = self._lib.mantis_undistort_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, _ptr(Kf), _ptr(Dd), _ptr(out),
+                                              MEM_HOST)
+        self._check(rc, "mantis_undistort_batch")
+        return out
+
+    # -- MarkovModel, include/mantis3/Markov.cpp --
+    MARKOV_INIT, MARKOV_CONVOLVE, MARKOV_SENSE = 0, 1, 2
+
+    def markov(self, planes, op, a, b=None):
+        """planes [S,360] float64 (updated copy returned); a, b per-stream arguments of the operation."""
+        planes = np.ascontiguousarray(planes, np.float64).copy()
+        a = np.ascontiguousarray(a, np.float64)
+        b = None if b is None else np.ascontiguousarray(b, np.float64)
+        rc = self._lib.mantis_markov_batch(self._h, _ptr(planes), len(planes), int(op), _ptr(a), _ptr(b), MEM_HOST)
+        self._check(rc, "mantis_markov_batch")
+        return planes
+
+    def markov_update_errors(self, planes, stream_of, yaw, err):
+        planes = np.ascontiguousarray(planes, np.float64)
+        so = np.ascontiguousarray(stream_of, np.int32)
+        yaw = np.ascontiguousarray(yaw, np.float64)
+        err = np.ascontiguousarray(err, np.float64).copy()
+        rc = self._lib.mantis_markov_update_errors(self._h, _ptr(planes), len(planes), _ptr(so), _ptr(yaw), _ptr(err),
+                                                   len(err), MEM_HOST)
+        self._check(rc, "mantis_markov_update_errors")
+        return err
 
     # -- quadDetection(), src/mantis3.cpp:68-135 --
     def set_map(self, white, red, green):

@@ -34,6 +34,8 @@ struct mantis_ctx {
     DevBuf quad_hyp, pose_offs;
     DevBuf cams, hyps, sel, pose_info, results, traces, mask_bits;  // localize scratch (per chunk)
     DevBuf render_poses;
+    DevBuf leg_a, leg_b, leg_c;              // scratch of the legacy-generation entry points (legacy.cu)
+    int n_red = 0;
     DevBuf pnp_stage;                        // host-caller staging of mantis_pnp_batch
     DevBuf hough_trig, hough_count, hough_peaks, hough_lines;  // line-voting stage (hough.cu)
     DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts

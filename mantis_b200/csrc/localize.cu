@@ -94,6 +94,7 @@ extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int
     if (rc) return rc;
     c->n_map = n;
     c->n_green = n_green;
+    c->n_red = n_red;
     c->map_planar = 1;
     for (int i = 0; i < n; ++i)
         if (xyz[3 * i + 2] != 0.0) c->map_planar = 0;

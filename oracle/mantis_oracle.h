@@ -72,6 +72,19 @@ void mo_rodrigues_log(const double* R, double* w);
 int mo_pnp_iterative(const float* obj, const float* img, int m, const float* K, const double* guess6, int flags,
                      int max_iters, double* out9);
 
+/* ---- legacy particle weight, fisheye::undistortImage, Markov yaw filter (oracle/legacy.c) ---- */
+void mo_markov_update_weights(double* yaw360, double stddev);
+void mo_markov_init(double* p360, double yaw_rad);
+void mo_markov_convolve(double* p360, double dtheta, double dt);
+void mo_markov_sense(double* p360, double yaw_rad);
+void mo_markov_update_errors(const double* p360, const double* yaw_rad, double* err, int n);
+double mo_markov_get_yaw(const double* p360, int* bin);
+double mo_camera_error(const uint8_t* img, int w, int h, int stride, const float* K, const double* w2c12, const double* map,
+                       int n_white, int n_red, int n_green);
+void mo_fisheye_undistort_maps(const float* K, const double* D, int w, int h, short* map1, unsigned short* map2);
+void mo_remap_linear_bgr(const uint8_t* src, int w, int h, int stride, const short* map1, const unsigned short* map2,
+                         uint8_t* dst, int dst_stride);
+
 /* ---- synthetic frame source (stands in for GridRenderer.cpp:211-353) ---- */
 void mo_render_grid(const double* R_w2c, const double* t_w2c, const float* K, const double* D, int w, int h,
                     double line_width, int floor_level, uint8_t* bgr);

@@ -380,3 +380,77 @@ def rodrigues_exp(w):
     w = np.ascontiguousarray(w, np.float64)
     f(w.ctypes.data, R.ctypes.data)
     return R.reshape(3, 3)
+
+
+# ---- SURVEY 8(f) rows 3-4 (oracle/legacy.c) ----
+def undistort_image(bgr, K, D):
+    """cv::fisheye::undistortImage(img, K, D, Knew=K) (MonteCarlo.cpp:284)."""
+    bgr, p = _u8(bgr)
+    h, w, _ = bgr.shape
+    Kf = np.ascontiguousarray(K, np.float32).reshape(-1)
+    Dd = np.ascontiguousarray(D, np.float64).reshape(-1)
+    m1 = np.zeros((h, w, 2), np.int16)
+    m2 = np.zeros((h, w), np.uint16)
+    f = lib().mo_fisheye_undistort_maps
+    f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    f(Kf.ctypes.data, Dd.ctypes.data, w, h, m1.ctypes.data, m2.ctypes.data)
+    out = np.zeros_like(bgr)
+    g = lib().mo_remap_linear_bgr
+    g.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                  ctypes.c_int]
+    g(p, w, h, 3 * w, m1.ctypes.data, m2.ctypes.data, out.ctypes.data, 3 * w)
+    return out, m1, m2
+
+
+def camera_error(bgr, K, w2c12, white, red, green):
+    """MonteCarlo::computeCameraError (MonteCarlo.cpp:183-226); w2c12 = R row-major (9) + t (3)."""
+    bgr, p = _u8(bgr)
+    h, w, _ = bgr.shape
+    Kf = np.ascontiguousarray(K, np.float32).reshape(-1)
+    T = np.ascontiguousarray(w2c12, np.float64).reshape(12)
+    mp = np.ascontiguousarray(np.concatenate([white, red, green]), np.float64)
+    f = lib().mo_camera_error
+    f.restype = ctypes.c_double
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                  ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    return f(p, w, h, 3 * w, Kf.ctypes.data, T.ctypes.data, mp.ctypes.data, len(white), len(red), len(green))
+
+
+class Markov:
+    """MarkovModel (include/mantis3/Markov.cpp) on one 360-bin plane."""
+
+    def __init__(self, yaw_rad=None, plane=None):
+        self.p = np.zeros(360, np.float64) if plane is None else np.ascontiguousarray(plane, np.float64).copy()
+        if yaw_rad is not None:
+            self._call("mo_markov_init", float(yaw_rad))
+
+    def _call(self, name, *a):
+        f = getattr(lib(), name)
+        f.argtypes = [ctypes.c_void_p] + [ctypes.c_double] * len(a)
+        f.restype = None
+        f(self.p.ctypes.data, *a)
+
+    def update_weights(self, stddev):
+        self._call("mo_markov_update_weights", float(stddev))
+
+    def convolve(self, dtheta, dt):
+        self._call("mo_markov_convolve", float(dtheta), float(dt))
+
+    def sense(self, yaw_rad):
+        self._call("mo_markov_sense", float(yaw_rad))
+
+    def update_errors(self, yaw_rad, err):
+        y = np.ascontiguousarray(yaw_rad, np.float64)
+        e = np.ascontiguousarray(err, np.float64).copy()
+        f = lib().mo_markov_update_errors
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+        f.restype = None
+        f(self.p.ctypes.data, y.ctypes.data, e.ctypes.data, len(e))
+        return e
+
+    def get_yaw(self):
+        b = ctypes.c_int()
+        f = lib().mo_markov_get_yaw
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        f.restype = ctypes.c_double
+        return f(self.p.ctypes.data, ctypes.byref(b)), b.value

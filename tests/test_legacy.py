@@ -1,0 +1,104 @@
+"""the 2016 generation's particle weight + undistortImage, and the Markov yaw filter.
+CPU: the oracle against cv2.fisheye.undistortImage (bit-exact) and closed-form properties of the filter.
+GPU: the CUDA entry points against the oracle."""
+import numpy as np
+import pytest
+
+from cases import all_cases
+from frames import D_UNIT, K_for, poses
+from oracle import pyoracle as po
+
+K_LENA = np.array([[200, 0, 256], [0, 200, 256], [0, 0, 1]], np.float32)
+
+
+def test_oracle_undistort_matches_cv2_bit_exact():
+    cv2 = pytest.importorskip("cv2")
+    for name, K in (("lena", K_LENA), ("grid1", np.array([[229.0, 0, 453.5], [0, 228.75, 252.5], [0, 0, 1]], np.float32))):
+        img = all_cases()[name]
+        ref = cv2.fisheye.undistortImage(img, K.astype(np.float64), D_UNIT, Knew=K.astype(np.float64))
+        out, m1, m2 = po.undistort_image(img, K, D_UNIT)
+        assert np.array_equal(ref, out)
+        r1, r2 = cv2.fisheye.initUndistortRectifyMap(K.astype(np.float64), D_UNIT, np.eye(3), K.astype(np.float64),
+                                                     (img.shape[1], img.shape[0]), cv2.CV_16SC2)
+        assert np.array_equal(r1, m1) and np.array_equal(r2, m2)
+
+
+def test_oracle_markov_properties():
+    m = po.Markov(yaw_rad=np.deg2rad(120.4))
+    assert abs(m.p.sum() - 1) < 1e-12 and m.get_yaw()[1] == 120
+    # Gaussian of sigma 3 around the bin: ratio of neighbours = exp(-1/18)
+    assert m.p[121] / m.p[120] == pytest.approx(np.exp(-1 / 18), rel=1e-9)
+    m.convolve(np.deg2rad(45), 5.0)          # (int)dTheta == 0: no shift, only diffusion (the reference's cast)
+    assert m.get_yaw()[1] == 120 and abs(m.p.sum() - 1) < 1e-12
+    m.convolve(1.2, 1.0)                     # (int)1.2 rad = 1 -> 57 bins
+    assert m.get_yaw()[1] == 177
+    m.sense(np.deg2rad(-170))                # bin 190
+    assert 177 < m.get_yaw()[1] <= 190
+    e = m.update_errors([np.deg2rad(185.5), np.deg2rad(10)], [2.0, 2.0])
+    assert e[0] == 2.0 / m.p[185] and e[1] > e[0]
+
+
+def _particles(n_p, seed):
+    rng = np.random.default_rng(seed)
+    out = []
+    for R, t in poses(n_p, seed=seed):
+        Rc, tc = R.T, -R.T @ t           # world -> camera
+        out.append(np.concatenate([Rc.reshape(-1), tc]))
+    return np.array(out) + rng.normal(0, 1e-3, (n_p, 12))
+
+
+def test_oracle_camera_error_counts_and_floor():
+    K = K_for(640, 480)
+    w, r, g = po.make_map()
+    img = np.full((480, 640, 3), 255, np.uint8)
+    T = _particles(1, 5)[0]
+    e = po.camera_error(img, K, T, w, r, g)
+    assert e >= 0 and e < 3 * 255 ** 2
+    behind = T.copy(); behind[9:] = [0, 0, -50]          # nothing in frame -> 1e17 / 0
+    far = po.camera_error(img, K, np.concatenate([np.eye(3).reshape(-1), [100, 100, 1]]), w, r, g)
+    assert far == np.inf or far >= 1e15
+
+
+@pytest.mark.gpu
+def test_cuda_undistort_matches_oracle(ctx):
+    for name, K in (("lena", K_LENA), ("odd_33x129", K_for(129, 33))):
+        img = all_cases()[name]
+        got = ctx.undistort(np.stack([img, img[::-1].copy()]), K, D_UNIT)
+        assert np.array_equal(got[0], po.undistort_image(img, K, D_UNIT)[0])
+        assert np.array_equal(got[1], po.undistort_image(img[::-1].copy(), K, D_UNIT)[0])
+
+
+@pytest.mark.gpu
+def test_cuda_particle_weights_match_oracle(ctx):
+    K, D = K_for(640, 480), np.zeros(4)
+    w, r, g = po.make_map()
+    frames = np.stack([po.render_grid(R, t, K, D, 640, 480) for R, t in poses(3, seed=31)])
+    P = np.stack([_particles(40, 100 + i) for i in range(3)])
+    P[0, 0] = np.concatenate([np.eye(3).reshape(-1), [100, 100, 1]])   # nothing projected
+    got = ctx.particle_weights(frames, K, P)
+    for i in range(3):
+        for k in range(40):
+            ref = po.camera_error(frames[i], K, P[i, k], w, r, g)
+            assert got[i, k] == ref or (np.isinf(ref) and np.isinf(got[i, k])), (i, k, got[i, k], ref)
+
+
+@pytest.mark.gpu
+def test_cuda_markov_matches_oracle(ctx):
+    yaws = np.deg2rad([120.4, -30.0, 359.2, 0.0, 181.0])
+    planes = ctx.markov(np.zeros((5, 360)), ctx.MARKOV_INIT, yaws)
+    ref = [po.Markov(yaw_rad=y) for y in yaws]
+    dth, dt = np.array([0.2, 1.2, -2.5, 3.1, -0.4]), np.array([0.5, 1.0, 2.0, 0.1, 5.0])
+    planes = ctx.markov(planes, ctx.MARKOV_CONVOLVE, dth, dt)
+    sense = np.deg2rad([118.0, 40.0, -5.0, 170.0, -179.0])
+    planes2 = ctx.markov(planes, ctx.MARKOV_SENSE, sense)
+    for i, m in enumerate(ref):
+        m.convolve(dth[i], dt[i])
+        assert np.allclose(planes[i], m.p, rtol=1e-10, atol=1e-300)
+        m.sense(sense[i])
+        assert np.allclose(planes2[i], m.p, rtol=1e-9, atol=1e-300)
+        assert abs(planes2[i].sum() - 1) < 1e-9
+    so = np.array([0, 0, 1, 4, 3], np.int32)
+    hy = np.deg2rad([119.0, 10.0, 41.0, -179.5, 171.0])
+    err = ctx.markov_update_errors(planes2, so, hy, np.full(5, 3.0))
+    for k in range(5):
+        assert err[k] == pytest.approx(ref[so[k]].update_errors([hy[k]], [3.0])[0], rel=1e-9)
