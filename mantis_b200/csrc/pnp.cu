@@ -203,7 +203,7 @@ __device__ int refine(const Corr& c, Pose& P, int max_iters, int lane, double* x
             P = Q;
             N = M;
             lambda = fmax(lambda * 0.1, 1e-15);
-            if (step < 1e-12 || gain <= 1e-15 * N.cost) break;
+            if (step < 1e-9 || gain <= 1e-12 * N.cost) break;
         } else {
             lambda *= 10;
             if (lambda > 1e12) break;

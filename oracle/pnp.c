@@ -197,7 +197,7 @@ static int pnp_refine(const float* obj, const float* img, int m, const double* K
             memcpy(R, Rn, sizeof(Rn)); memcpy(t, tn, sizeof(tn)); memcpy(A, An, sizeof(An)); memcpy(g, gn, sizeof(gn));
             cost = cn;
             lambda = fmax(lambda * 0.1, 1e-15);
-            if (step < 1e-12 || gain <= 1e-15 * cost) break;
+            if (step < 1e-9 || gain <= 1e-12 * cost) break;
         } else {
             lambda *= 10;
             if (lambda > 1e12) break;
