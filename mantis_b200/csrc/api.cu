@@ -72,6 +72,8 @@ int mantis_destroy(mantis_ctx* c)
     if (!c) return MANTIS_ERR_INVALID;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    for (int i = 0; i < mantis_ctx::MAX_LANES; ++i)
+        if (c->lane[i]) { mantis_destroy(c->lane[i]); c->lane[i] = nullptr; }
     DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_in2, &c->stage_out0,
                       &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->frame_quads,
                       &c->cams, &c->hyps, &c->sel, &c->pose_info, &c->results, &c->traces, &c->mask_bits,
@@ -128,7 +130,14 @@ int mantis_get_stage_ms(mantis_ctx* c, double* ms)
 }
 
 const char* mantis_last_error(const mantis_ctx* c) { return c ? c->err : ""; }
-uint64_t mantis_launch_count(const mantis_ctx* c) { return c ? c->launches : 0; }
+uint64_t mantis_launch_count(const mantis_ctx* c)
+{
+    if (!c) return 0;
+    uint64_t n = c->launches;
+    for (int i = 0; i < mantis_ctx::MAX_LANES; ++i)
+        if (c->lane[i]) n += c->lane[i]->launches;
+    return n;
+}
 void* mantis_stream(const mantis_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
 }  // extern "C"

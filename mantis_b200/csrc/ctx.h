@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <vector>
 #include "../../include/mantis_cuda.h"
 #include "pipeline.cuh"
 
@@ -40,6 +41,12 @@ struct mantis_ctx {
     DevBuf hough_trig, hough_count, hough_peaks, hough_lines;  // line-voting stage (hough.cu)
     DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts
     int n_map = 0, n_green = 0, n_shift = 0;
+    // two-lane execution of large device-resident batches (localize.cu): child contexts with their own
+    // streams and scratch, so that the latency-bound kernels of one half overlap the other half's
+    static constexpr int MAX_LANES = 4;
+    mantis_ctx* lane[MAX_LANES] = {};
+    bool is_lane = false;
+    std::vector<double> host_map;            // what mantis_set_map received (replayed into the lanes)
     int map_planar = 0;                      // every map point has z == 0 (the reference's floor grid)
     DevBuf d_atan;                           // (i pi/256, tan(i pi/256)) table of the fast fp64 atan (search.cu)
     Tf rotz;                                 // +90 degrees about z

@@ -3,6 +3,7 @@
 // perturbations, cell shifts).
 #include <stdlib.h>
 #include <new>
+#include <thread>
 #include <vector>
 #include "ctx.h"
 #include "cvrng.h"
@@ -95,6 +96,9 @@ extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int
     c->n_map = n;
     c->n_green = n_green;
     c->n_red = n_red;
+    c->host_map.assign(xyz, xyz + 3 * (size_t)n);
+    for (int i = 0; i < mantis_ctx::MAX_LANES; ++i)
+        if (c->lane[i] && (rc = mantis_set_map(c->lane[i], xyz, n_white, n_red, n_green))) return rc;
     c->map_planar = 1;
     for (int i = 0; i < n; ++i)
         if (xyz[3 * i + 2] != 0.0) c->map_planar = 0;
@@ -122,6 +126,36 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
             }
     }
     MCHECK(c, cudaSetDevice(c->device));
+
+    // Large device-resident batches are split over a few lanes (child contexts: own stream, own scratch;
+    // MANTIS_LANES, default 3) driven by one host thread each, so that the latency-bound kernels of one part (border walks,
+    // RPP iterations) share the SMs with whatever the other parts are running.  Per-stage profiling needs the
+    // stages back to back on one stream, so it keeps the single-lane path.
+    static const int lanes_env = []() { const char* e = getenv("MANTIS_LANES"); return e ? atoi(e) : 3; }();
+    const int L = lanes_env > mantis_ctx::MAX_LANES ? mantis_ctx::MAX_LANES : lanes_env;
+    if (mem == MANTIS_MEM_DEVICE && !c->is_lane && !c->profiling && L >= 2 && n >= 512 * L) {
+        for (int i = 0; i < L; ++i)
+            if (!c->lane[i]) {
+                int rc0 = mantis_create(&c->cfg, c->device, &c->lane[i]);
+                if (rc0) { snprintf(c->err, sizeof(c->err), "cannot create execution lane %d", i); return rc0; }
+                c->lane[i]->is_lane = true;
+                if (!c->host_map.empty() &&
+                    (rc0 = mantis_set_map(c->lane[i], c->host_map.data(), c->n_map - c->n_red - c->n_green, c->n_red, c->n_green)))
+                    return rc0;
+            }
+        int rcs[mantis_ctx::MAX_LANES] = {};
+        auto run = [&](int i) {
+            const int f0 = (int)((long long)n * i / L), f1 = (int)((long long)n * (i + 1) / L);
+            rcs[i] = mantis_localize_batch(c->lane[i], frames + f0, f1 - f0, out + f0, trace ? trace + f0 : nullptr, mem);
+        };
+        std::thread th[mantis_ctx::MAX_LANES];
+        for (int i = 1; i < L; ++i) th[i] = std::thread(run, i);
+        run(0);
+        for (int i = 1; i < L; ++i) th[i].join();
+        for (int i = 0; i < L; ++i)
+            if (rcs[i]) { snprintf(c->err, sizeof(c->err), "lane %d: %s", i, c->lane[i]->err); return rcs[i]; }
+        return MANTIS_OK;
+    }
 
     // frames per pass of the kernel chain: large enough that the latency-bound tails (longest border
     // walk, slowest RPP run) are amortised over many frames, small enough that the per-frame scratch
