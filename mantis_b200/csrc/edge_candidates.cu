@@ -13,7 +13,7 @@
 //   gray = (3735 B + 19235 G + 9798 R + 16384) >> 15
 //   blur = taps (84,88,84)/256 per axis, BORDER_REFLECT_101, (v + 32768) >> 16
 //   Sobel 3x3 on the blurred image with BORDER_REPLICATE; mag = |dx| + |dy|, 0 outside
-//   NMS: TG22 = 13573 (Q15) sector test, see nms_candidate().
+//   NMS: TG22 = 13573 (Q15) sector test (phase 3 below).
 //
 // Shape of the kernel (one CTA of 4 warps per 128 x 32 output tile; HBM-bound by design: 3 B/px in,
 // 2 bits/px out, every intermediate lives in shared memory as packed words of 4 px):
@@ -354,18 +354,13 @@ k_edge_candidates(const uint8_t* __restrict__ bgr, int W, int H, int stride, siz
         const int ax = abs(xs), ay = abs(ys) << 15;
         const int m = abs(xs) + abs(ys);
         const int tg22x = ax * 13573;
-        bool cand;
-        if (ay < tg22x) {
-            cand = (m > mag_of(c[-1])) && (m >= mag_of(c[1]));
-        } else {
-            const int tg67x = tg22x + (ax << 16);
-            if (ay > tg67x) {
-                cand = (m > mag_of(c[-DP])) && (m >= mag_of(c[DP]));
-            } else {
-                const int sgn = ((xs ^ ys) < 0) ? -1 : 1;
-                cand = (m > mag_of(c[-DP - sgn])) && (m > mag_of(c[DP + sgn]));
-            }
-        }
+        // sector -> the two neighbours to beat: horizontal (left strictly, right or equal), vertical (up
+        // strictly, down or equal), diagonal (both strictly); one pair of loads whatever the sector
+        const bool horiz = ay < tg22x, vert = ay > tg22x + (ax << 16);
+        const int sgn = ((xs ^ ys) < 0) ? -1 : 1;
+        const int o1 = horiz ? -1 : (vert ? -DP : -DP - sgn);
+        const int m1 = mag_of(c[o1]), m2 = mag_of(c[-o1]);
+        const bool cand = (m > m1) && ((horiz || vert) ? (m >= m2) : (m > m2));
         if (cand) {
             const int wi = ty * (TW / 32) + (tx >> 5);
             const uint32_t bit = 1u << (tx & 31);
