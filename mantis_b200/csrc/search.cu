@@ -215,16 +215,49 @@ __device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map
     int e_acc = 0, ok_acc = 0;
     PoseXY c2w;
     if (t_begin < t_end) c2w = load_pose(get(h));
+    // Three-stage software pipeline over the tasks of this warp, so that the two dependent gathers of a
+    // point (mask word, then pixel bytes) are in flight while the next points are being projected:
+    //   stage 1 (task t)    project, issue the mask-word load
+    //   stage 2 (task t-1)  test the mask bit, issue the pixel loads
+    //   stage 3 (task t-2)  add the colour error
+    uint32_t m_word = 0;
+    int m_key = -1;  // (pixel byte offset << 5) | mask bit, -1 = nothing pending
+    int pb = 255, pg = 255, pr = 255;  // pixel bytes in flight; white = no contribution
+    auto stage3 = [&]() {
+        const int db = pb - 255, dg = pg - 255, dr = pr - 255;
+        e_acc += db * db + dg * dg + dr * dr;
+        pb = pg = pr = 255;
+    };
+    auto stage2 = [&]() {
+        if (m_key >= 0) {
+            pb = pg = pr = 0;
+            if ((m_word >> (m_key & 31)) & 1u) {
+                const uint8_t* p = im.bgr + ((unsigned)m_key >> 5);
+                pb = __ldg(p); pg = __ldg(p + 1); pr = __ldg(p + 2);
+            }
+            m_key = -1;
+        }
+    };
     for (int t = t_begin; t < t_end; ++t) {
+        stage3();
+        stage2();
         const int pi = ch * 32 + lane;
         if (pi < n_map) {
             double u, v;
             if (project(c2w, cam, s.map_x[pi], s.map_y[pi], planar ? 0.0 : s.map_z[pi], planar, s.atan_tab, im.W, im.H, u, v)) {
                 ++ok_acc;
-                e_acc += pixel_err(im, __double2int_rn(u), __double2int_rn(v), true, 255, 255, 255);
+                const int x = __double2int_rn(u), y = __double2int_rn(v);
+                const unsigned off = (unsigned)(y * im.stride + 3 * x);
+                if ((unsigned)x < (unsigned)im.W && (unsigned)y < (unsigned)im.H && off < (1u << 26)) {
+                    m_word = __ldg(im.mask + (unsigned)(y * im.WW + (x >> 5)));
+                    m_key = (int)(off << 5) | (x & 31);
+                } else {  // x == W or y == H (the reference's linear addressing), or a frame beyond 64 MB
+                    e_acc += pixel_err(im, x, y, true, 255, 255, 255);  // x == W or y == H: the reference's linear addressing
+                }
             }
         }
         if (++ch == chunks || t + 1 == t_end) {
+            stage3(); stage2(); stage3();  // drain: everything pending belongs to hypothesis h
             const int e = __reduce_add_sync(0xffffffffu, e_acc), ok = __reduce_add_sync(0xffffffffu, ok_acc);
             if (lane == 0 && ok) {
                 atomicAdd(&s.sum[h], (unsigned long long)e);
