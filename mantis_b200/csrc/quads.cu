@@ -23,8 +23,15 @@
 //             RETR_CCOMP), then approxPolyDP (OpenCV 4.13 variant: distance to the SEGMENT).
 //   k_qfinish per frame: hole parents, CCOMP ordering (outer borders in reverse discovery order,
 //             each followed by its holes, reversed), Quadrilateral ctor, de-duplication, output.
+// That is the fallback.  Frames whose bit plane fits in shared memory take the segment-parallel
+// route (k_qcut, k_qseg, k_qlink, k_qemit below): borders are cut into short pieces that are walked
+// independently and linked afterwards, so no thread ever follows a whole border.
 // A walk step is branch-light: the 3x3 neighbourhood comes from three word loads, the next
 // direction from a rotate + find-first-set on the 8-bit neighbour mask.
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
 #include "ctx.h"
 #include "pipeline.cuh"
 
@@ -369,7 +376,7 @@ __device__ int approx_poly_closed_warp(const short2* src, int count, double eps,
 }
 
 struct QMeta {  // per frame, zeroed before every batch
-    int ncand, nstart, flags, nb, nlong, pad_[3];
+    int ncand, nstart, flags, nb, nlong, ncut, fallback, ncc;
 };
 constexpr int LONG_NP = 96;   // contours with more vertices are handled by a whole warp
 constexpr int MAXLONG = MANTIS_MAX_PTS / LONG_NP + 1;
@@ -393,6 +400,12 @@ struct QuadArgs {
     short2* dst;          // [n][MANTIS_MAX_PTS]
     int2* stack;          // [n][MANTIS_MAX_PTS + 2 * MAXB]
     uint16_t* owner;      // [n][W * H]
+    uint32_t* cut;        // [n][MAXCUT] cut visits as listed by k_qcut (pixel, side, candidate)
+    uint32_t* cut_key;    // [n][MAXCUT] visit keys (pixel << 3 | back direction) + KEY_ flags, from k_qseg
+    uint32_t* cut_end;    // [n][MAXCUT] state at which the piece starting here ends
+    int* cut_np;          // [n][MAXCUT] CHAIN_APPROX_SIMPLE vertices of the piece
+    uint32_t* cut_dst;    // [n][MAXCUT] (offset of the piece's vertices in its frame << 10) | border
+    int use_cuts;
     FrameQuads* out;
     double eps, stretch, radius_mult;
 };
@@ -411,31 +424,21 @@ __device__ __forceinline__ int ones_from0(uint32_t t)
 }
 
 // ---- 1. candidates -------------------------------------------------------------------------
-__global__ void __launch_bounds__(CNT) k_qcand(QuadArgs a)
+// Border-start candidates among the pixels of word j of row y (c = that word): push(is_hole, x).
+template <class F>
+__device__ __forceinline__ void word_candidates(const uint32_t* bits, int W, int H, int WW, int y, int j, uint32_t c, F push)
 {
-    const int W = a.W, H = a.H, WW = a.WW, frame = blockIdx.y;
-    const int i = blockIdx.x * CNT + threadIdx.x;
-    if (i >= H * WW) return;
-    const uint32_t* bits = a.morph_bits + (size_t)frame * H * WW;
-    const int y = i / WW, j = i - y * WW;
-    const uint32_t c = bits_at(bits, WW, H, y, j), cp = bits_at(bits, WW, H, y, j - 1);
+    const uint32_t cp = bits_at(bits, WW, H, y, j - 1);
     const uint32_t left = (c << 1) | (cp >> 31);
     const uint32_t valid = (j == WW - 1 && (W & 31)) ? ((1u << (W & 31)) - 1u) : 0xffffffffu;
     uint32_t outer = c & ~left;                          // first pixels of foreground runs
     uint32_t hole = (y > 0) ? (~c & left & valid) : 0u;  // first pixels of background runs right of foreground
     if (!(outer | hole)) return;
-    QMeta* meta = a.meta + frame;
 
     auto dilated_above = [&](int jj) {  // foreground of row y-1 at columns p-1, p, p+1, for the columns p of word jj
         uint32_t u = bits_at(bits, WW, H, y - 1, jj);
         return u | (u << 1) | (bits_at(bits, WW, H, y - 1, jj - 1) >> 31) | (u >> 1) | (bits_at(bits, WW, H, y - 1, jj + 1) << 31);
     };
-    auto push = [&](uint32_t v) {
-        int k = atomicAdd(&meta->ncand, 1);
-        if (k < MAXCAND) a.cand[(size_t)frame * MAXCAND + k] = v;
-        else atomicOr(&meta->flags, FRAME_FLAG_BORDER_OVERFLOW);
-    };
-
     while (outer) {
         const int b = __ffs(outer) - 1;
         outer &= outer - 1;
@@ -452,7 +455,7 @@ __global__ void __launch_bounds__(CNT) k_qcand(QuadArgs a)
             w = bits_at(bits, WW, H, y, jj);
             if (!(w & 1u)) break;
         }
-        if (ok) push(((uint32_t)y << 15) | (uint32_t)(j * 32 + b));
+        if (ok) push(false, j * 32 + b);
     }
     while (hole) {
         const int b = __ffs(hole) - 1;
@@ -473,7 +476,23 @@ __global__ void __launch_bounds__(CNT) k_qcand(QuadArgs a)
             w = ~bits_at(bits, WW, H, y, jj);
             if (!(w & 1u)) break;
         }
-        if (ok) push(0x80000000u | ((uint32_t)y << 15) | (uint32_t)(j * 32 + b));
+        if (ok) push(true, j * 32 + b);
+    }
+}
+
+__global__ void __launch_bounds__(CNT) k_qcand(QuadArgs a)
+{
+    const int W = a.W, H = a.H, WW = a.WW, frame = blockIdx.y;
+    QMeta* meta = a.meta + frame;
+    if (a.use_cuts && !meta->fallback) return;
+    const uint32_t* bits = a.morph_bits + (size_t)frame * H * WW;
+    for (int i = blockIdx.x * CNT + threadIdx.x; i < H * WW; i += gridDim.x * CNT) {
+        const int y = i / WW, j = i - y * WW;
+        word_candidates(bits, W, H, WW, y, j, bits_at(bits, WW, H, y, j), [&](bool is_hole, int x) {
+            int k = atomicAdd(&meta->ncand, 1);
+            if (k < MAXCAND) a.cand[(size_t)frame * MAXCAND + k] = (is_hole ? 0x80000000u : 0u) | ((uint32_t)y << 15) | (uint32_t)x;
+            else atomicOr(&meta->flags, FRAME_FLAG_BORDER_OVERFLOW);
+        });
     }
 }
 
@@ -528,6 +547,7 @@ __device__ __forceinline__ void probe_frame(const QuadArgs& a, const Img& im, in
 __global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a, int use_smem)
 {
     const int frame = blockIdx.x;
+    if (a.use_cuts && !a.meta[frame].fallback) return;
     const uint32_t* g = a.morph_bits + (size_t)frame * a.H * a.WW;
     if (use_smem) {
         probe_frame(a, stage_padded(g, a.H, a.WW), frame);
@@ -539,43 +559,55 @@ __global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a, int use_smem)
 }
 
 // ---- 3. discovery order, point offsets, by-length order ---------------------------------------
-__global__ void __launch_bounds__(CNT) k_qrank(QuadArgs a)
+struct RankSmem {
+    uint32_t ukey[MAXB];
+    int ust[MAXB], np[MAXB], st[MAXB];
+};
+// Ranks the frame's starts a.ukey/unp/usteps[0..nb) (global).  rank_of (shared, may be null)
+// receives the discovery index of every unsorted start.
+__device__ void rank_frame(const QuadArgs& a, int frame, RankSmem& r, int nb, short* rank_of)
 {
-    __shared__ uint32_t s_ukey[MAXB];
-    __shared__ int s_ust[MAXB];
-    __shared__ int s_np[MAXB], s_st[MAXB];
-    const int frame = blockIdx.x, tid = threadIdx.x;
+    const int tid = threadIdx.x, nt = blockDim.x;
     QMeta* meta = a.meta + frame;
-    const int nb = min(meta->nstart, MAXB);
     const size_t base = (size_t)frame * MAXB;
-    for (int i = tid; i < nb; i += CNT) { s_ukey[i] = a.ukey[base + i]; s_ust[i] = a.usteps[base + i]; }
+    for (int i = tid; i < nb; i += nt) { r.ukey[i] = a.ukey[base + i]; r.ust[i] = a.usteps[base + i]; }
     __syncthreads();
-    for (int i = tid; i < nb; i += CNT) {
-        const uint32_t k = s_ukey[i];
-        int r = 0;
-        for (int j = 0; j < nb; ++j) r += s_ukey[j] < k;
-        a.key[base + r] = k;
-        s_np[r] = a.unp[base + i];
-        s_st[r] = s_ust[i];
+    for (int i = tid; i < nb; i += nt) {
+        const uint32_t k = r.ukey[i];
+        int rk = 0;
+        for (int j = 0; j < nb; ++j) rk += r.ukey[j] < k;
+        a.key[base + rk] = k;
+        r.np[rk] = a.unp[base + i];
+        r.st[rk] = r.ust[i];
+        if (rank_of) rank_of[i] = (short)rk;
     }
     __syncthreads();
     if (tid == 0) {
         int acc = 0;
-        for (int i = 0; i < nb; ++i) { a.off[base + i] = acc; acc += s_np[i]; }
+        for (int i = 0; i < nb; ++i) { a.off[base + i] = acc; acc += r.np[i]; }
         if (acc > MANTIS_MAX_PTS) meta->flags |= FRAME_FLAG_POINT_OVERFLOW;
         meta->nb = nb;
     }
-    for (int i = tid; i < nb; i += CNT) {
-        a.np[base + i] = s_np[i];
-        const int st = s_st[i];
-        int r = 0;  // position by descending walk length (ties by index)
-        for (int j = 0; j < nb; ++j) r += (s_st[j] > st) || (s_st[j] == st && j < i);
-        a.bylen[base + r] = (short)i;
-        if (s_np[i] > LONG_NP) {
+    for (int i = tid; i < nb; i += nt) {
+        a.np[base + i] = r.np[i];
+        const int st = r.st[i];
+        int rk = 0;  // position by descending walk length (ties by index)
+        for (int j = 0; j < nb; ++j) rk += (r.st[j] > st) || (r.st[j] == st && j < i);
+        a.bylen[base + rk] = (short)i;
+        if (r.np[i] > LONG_NP) {
             int k = atomicAdd(&meta->nlong, 1);
             if (k < MAXLONG) a.longl[(size_t)frame * MAXLONG + k] = (short)i;
         }
     }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(CNT) k_qrank(QuadArgs a)
+{
+    __shared__ RankSmem r;
+    const int frame = blockIdx.x;
+    if (a.use_cuts && !a.meta[frame].fallback) return;
+    rank_frame(a, frame, r, min(a.meta[frame].nstart, MAXB), nullptr);
 }
 
 // ---- 4. extraction + approxPolyDP, one thread per border --------------------------------------
@@ -609,6 +641,7 @@ __device__ __forceinline__ void trace_frame(const QuadArgs& a, const Img& im, in
 __global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a, int use_smem)
 {
     const int frame = blockIdx.x;
+    if (a.use_cuts && !a.meta[frame].fallback) return;
     const uint32_t* g = a.morph_bits + (size_t)frame * a.H * a.WW;
     if (use_smem) {
         if (a.meta[frame].flags || a.meta[frame].nb == 0) return;
@@ -620,6 +653,317 @@ __global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a, int use_smem)
     }
 }
 
+// ---- segment-parallel tracing -----------------------------------------------------------------
+// A border is a cycle of VISITS (pixel, direction back to the previous pixel); a visit examines one
+// maximal run of background neighbours, and every background 4-neighbour of a foreground pixel is
+// examined by exactly one visit of exactly one border.  A visit can therefore be recognised from its
+// pixel's 3x3 neighbourhood alone, and borders can be cut at visits that are listed without walking:
+//   candidates  the visit examining West of an outer-border candidate pixel, and the visit
+//               examining East of the pixel left of a hole candidate (the run tests of k_qcand);
+//               a border's start is the raster-first candidate visit of its cycle, and that
+//               candidate's kind says whether the cycle is an outer or a hole border,
+//   rows        every visit examining West or East on the rows y % CUT_ROWS == 0 (bounds the pieces).
+//   k_qcut   lists the cut visits of a frame, bit-parallel.
+//   k_qseg   one thread per cut: walks to the next cut, counting CHAIN_APPROX_SIMPLE vertices.
+//   k_qlink  per frame: links the pieces into cycles (hash of visit keys), finds every cycle's
+//            start, ranks the starts in discovery order, gives every piece its place in the vertex array.
+//   k_qemit  one thread per cut: second walk, writing vertices and left-edge owners.
+// approxPolyDP then runs per border (k_qapprox_long).  A frame that exceeds MAXCUT / MAXCC, or whose
+// links do not close, is handed to the sequential-walk kernels above (meta->fallback).
+constexpr int CUT_ROWS = 16;
+constexpr int MAXCUT = 2048;   // cut visits per frame
+constexpr int MAXCC = 512;     // candidates among them
+constexpr int TABN = 2048;     // candidate table (open addressing)
+constexpr int HASHN = 4096;
+constexpr uint32_t KEY_LTOP = 1u << 30, KEY_RCAND = 1u << 31, KEY_STATE = 0x00ffffffu, KEY_DEAD = 0x0f000000u;
+constexpr uint32_t EMPTY = 0xffffffffu;
+
+// candidate visits of the frame, keyed (pixel << 1) | (1 if it is the East side)
+struct CutSet {
+    uint32_t* tab;  // [TABN], shared
+    int W;
+    static __device__ __forceinline__ uint32_t slot(uint32_t k) { return (k * 2654435761u) >> 21; }  // TABN = 2^11
+    __device__ __forceinline__ void insert(uint32_t k)
+    {
+        for (uint32_t h = slot(k);; h = (h + 1) & (TABN - 1)) {
+            const uint32_t old = atomicCAS(&tab[h], EMPTY, k);
+            if (old == EMPTY || old == k) return;
+        }
+    }
+    __device__ __forceinline__ bool has(uint32_t k) const
+    {
+        for (uint32_t h = slot(k);; h = (h + 1) & (TABN - 1)) {
+            const uint32_t t = tab[h];
+            if (t == k) return true;
+            if (t == EMPTY) return false;
+        }
+    }
+    __device__ __forceinline__ bool cand_west(int x, int y, uint32_t nb) const { return (nb & 0x0eu) == 0u && has((uint32_t)(y * W + x) << 1); }
+    __device__ __forceinline__ bool cand_east(int x, int y, uint32_t nb) const { return (nb & 0x02u) != 0u && has(((uint32_t)(y * W + x) << 1) | 1u); }
+    __device__ __forceinline__ bool cut_west(int x, int y, uint32_t nb) const { return (y & (CUT_ROWS - 1)) == 0 || cand_west(x, y, nb); }
+    __device__ __forceinline__ bool cut_east(int x, int y, uint32_t nb) const { return (y & (CUT_ROWS - 1)) == 0 || cand_east(x, y, nb); }
+    // is the visit at (x, y) that examined the background directions z a cut?
+    __device__ __forceinline__ bool is_cut(int x, int y, uint32_t nb, uint32_t z) const
+    {
+        return ((z & 0x10u) && cut_west(x, y, nb)) || ((z & 0x01u) && cut_east(x, y, nb));
+    }
+};
+
+// raw entries: (pixel << 2) | (2 if East side) | (1 if candidate)
+__global__ void __launch_bounds__(CNT) k_qcut(QuadArgs a)
+{
+    const int W = a.W, H = a.H, WW = a.WW, frame = blockIdx.y;
+    const uint32_t* bits = a.morph_bits + (size_t)frame * H * WW;
+    QMeta* meta = a.meta + frame;
+    uint32_t* dst = a.cut + (size_t)frame * MAXCUT;
+    for (int i = blockIdx.x * CNT + threadIdx.x; i < H * WW; i += gridDim.x * CNT) {
+        const uint32_t c = __ldg(bits + i);
+        const int y = i / WW, j = i - y * WW;
+        word_candidates(bits, W, H, WW, y, j, c, [&](bool is_hole, int x) {
+            const int k = atomicAdd(&meta->ncut, 1);
+            if (atomicAdd(&meta->ncc, 1) >= MAXCC || k >= MAXCUT) { meta->fallback = 1; return; }
+            dst[k] = is_hole ? ((((uint32_t)(y * W + x - 1)) << 2) | 3u) : ((((uint32_t)(y * W + x)) << 2) | 1u);
+        });
+        if (!c || (y & (CUT_ROWS - 1))) continue;
+        const uint32_t cp = bits_at(bits, WW, H, y, j - 1), cn = bits_at(bits, WW, H, y, j + 1);
+        uint32_t west = c & ~((c << 1) | (cp >> 31));   // foreground with background to the West
+        uint32_t east = c & ~((c >> 1) | (cn << 31));   // ... to the East
+        const int n = __popc(west) + __popc(east);
+        int k = atomicAdd(&meta->ncut, n);
+        if (k + n > MAXCUT) { meta->fallback = 1; continue; }
+        const uint32_t pos0 = (uint32_t)(y * W + j * 32);
+        while (west) { const int b = __ffs(west) - 1; west &= west - 1; dst[k++] = (pos0 + b) << 2; }
+        while (east) { const int b = __ffs(east) - 1; east &= east - 1; dst[k++] = ((pos0 + b) << 2) | 2u; }
+    }
+}
+
+struct SegCount {
+    int np;
+    __device__ __forceinline__ void visit(int, int, uint32_t) {}
+    __device__ __forceinline__ void point(int, int) { ++np; }
+};
+struct SegEmit {
+    short2* out;
+    uint16_t* owner;
+    int W;
+    uint16_t id;
+    __device__ __forceinline__ void visit(int x, int y, uint32_t z)
+    {
+        if (z & 0x10u) owner[(size_t)y * W + x] = id;  // this border owns the left edge of (x, y)
+    }
+    __device__ __forceinline__ void point(int x, int y) { *out++ = make_short2((short)x, (short)y); }
+};
+
+// Walks from the visit (x, y, s) -- s = direction back to the previous pixel, nb = neighbour mask of
+// (x, y), not empty -- to the next cut visit and returns that visit's key.  The steps are those of
+// follow_border; the first visit is processed without asking whether it is a cut.
+template <class Img, class V>
+__device__ __forceinline__ uint32_t walk_piece(const Img& im, const CutSet& cs, int x, int y, int s, uint32_t nb, V& vis)
+{
+    int prev_s = s ^ 4;
+    bool first = true;
+    for (int guard = 0; guard < (1 << 22); ++guard) {
+        const int r0 = (s + 1) & 7;
+        const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
+        const int k = __ffs(rot) - 1;
+        uint32_t z = ((1u << k) - 1u) << r0;
+        z = (z | (z >> 8)) & 0xffu;
+        if (!first && cs.is_cut(x, y, nb, z)) return ((uint32_t)(y * cs.W + x) << 3) | (uint32_t)s;
+        first = false;
+        s = (r0 + k) & 7;
+        vis.visit(x, y, z);
+        if (s != prev_s) {
+            vis.point(x, y);
+            prev_s = s;
+        }
+        x += dir_dx(s);
+        y += dir_dy(s);
+        s = (s + 4) & 7;
+        nb = im.nbr(x, y);
+    }
+    return EMPTY;  // no cut met: k_qlink finds no such visit and hands the frame to the sequential route
+}
+
+// direction of the first foreground neighbour clockwise from `side` (nb not empty, `side` background)
+__device__ __forceinline__ int back_dir(uint32_t nb, int side)
+{
+    const uint32_t rot = ((nb | (nb << 8)) >> side) & 0xffu;  // bit j: direction side + j
+    return (side + 31 - __clz((int)rot)) & 7;
+}
+
+__global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
+{
+    __shared__ uint32_t s_tab[TABN];
+    const int frame = blockIdx.x, W = a.W;
+    QMeta* meta = a.meta + frame;
+    if (meta->fallback) return;
+    const int ncut = meta->ncut;
+    const size_t base = (size_t)frame * MAXCUT;
+    CutSet cs{s_tab, W};
+    for (int i = threadIdx.x; i < TABN; i += CNT) s_tab[i] = EMPTY;
+    __syncthreads();
+    for (int i = threadIdx.x; i < ncut; i += CNT) {
+        const uint32_t raw = a.cut[base + i];
+        if (raw & 1u) cs.insert(raw >> 1);
+    }
+    const PadImg im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
+    for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
+        const uint32_t raw = a.cut[base + slot];
+        const bool east = raw & 2u;
+        const int side = east ? 0 : 4, pos = (int)(raw >> 2), y = pos / W, x = pos - y * W;
+        const uint32_t nb = im.nbr(x, y);
+        uint32_t key = KEY_DEAD, end = 0;
+        int np = 0;
+        if (!(raw & 1u) && cs.has(raw >> 1)) {
+            // a row cut that is also listed as a candidate: the candidate entry stands for it
+        } else if (nb == 0u) {  // isolated pixel: one visit, one vertex; stands under its West side
+            if (!east) { key = ((uint32_t)pos << 3) | KEY_LTOP; end = (uint32_t)pos << 3; np = 1; }
+        } else {
+            const int s = back_dir(nb, side), r0 = (s + 1) & 7;
+            const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
+            uint32_t z = ((1u << (__ffs(rot) - 1)) - 1u) << r0;
+            z = (z | (z >> 8)) & 0xffu;
+            if (!(east && (z & 0x10u) && cs.cut_west(x, y, nb))) {  // else the same visit stands under its West side
+                key = ((uint32_t)pos << 3) | (uint32_t)s;
+                if ((z & 0x10u) && cs.cand_west(x, y, nb)) key |= KEY_LTOP;
+                if ((z & 0x01u) && cs.cand_east(x, y, nb)) key |= KEY_RCAND;
+                SegCount v{0};
+                end = walk_piece(im, cs, x, y, s, nb, v);
+                np = v.np;
+            }
+        }
+        if (np > 65535) meta->fallback = 1;
+        a.cut_key[base + slot] = key;
+        a.cut_end[base + slot] = end;
+        a.cut_np[base + slot] = np;
+    }
+}
+
+constexpr int LNT = 256;
+__global__ void __launch_bounds__(LNT) k_qlink(QuadArgs a)
+{
+    __shared__ uint32_t s_key[MAXCUT];
+    __shared__ uint16_t s_succ[MAXCUT], s_np[MAXCUT];
+    __shared__ short s_start[MAXB], s_rank[MAXB];
+    __shared__ union U {
+        struct { uint32_t key[HASHN]; uint16_t val[HASHN]; } h;
+        RankSmem r;
+        __device__ U() {}
+    } u;
+    __shared__ int s_bad, s_nstart;
+
+    const int frame = blockIdx.x, tid = threadIdx.x, W = a.W;
+    QMeta* meta = a.meta + frame;
+    if (meta->fallback) return;
+    const int ncut = meta->ncut;
+    const size_t base = (size_t)frame * MAXCUT, bbase = (size_t)frame * MAXB;
+    for (int i = tid; i < HASHN; i += LNT) u.h.key[i] = EMPTY;
+    for (int i = tid; i < ncut; i += LNT) {
+        s_key[i] = a.cut_key[base + i];
+        s_np[i] = (uint16_t)a.cut_np[base + i];
+        a.cut_dst[base + i] = EMPTY;
+    }
+    if (tid == 0) { s_bad = 0; s_nstart = 0; }
+    __syncthreads();
+    auto slot_of = [](uint32_t st) { return (st * 2654435761u) >> 20; };  // HASHN = 2^12
+    for (int i = tid; i < ncut; i += LNT) {
+        const uint32_t k = s_key[i];
+        if (k & KEY_DEAD) continue;
+        const uint32_t st = k & KEY_STATE;
+        for (uint32_t h = slot_of(st);; h = (h + 1) & (HASHN - 1)) {
+            const uint32_t old = atomicCAS(&u.h.key[h], EMPTY, st);
+            if (old == EMPTY) { u.h.val[h] = (uint16_t)i; break; }
+            if (old == st) { s_bad = 1; break; }  // one visit listed twice: not expected
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < ncut; i += LNT) {
+        if (s_key[i] & KEY_DEAD) continue;
+        const uint32_t st = a.cut_end[base + i];
+        uint32_t h = slot_of(st);
+        for (;; h = (h + 1) & (HASHN - 1)) {
+            const uint32_t k = u.h.key[h];
+            if (k == st || k == EMPTY) break;
+        }
+        if (u.h.key[h] == st) s_succ[i] = u.h.val[h];
+        else s_bad = 1;  // the piece ended at a visit nobody listed
+    }
+    __syncthreads();
+    if (s_bad) { if (tid == 0) meta->fallback = 1; return; }
+    // every cycle's start: its raster-first candidate visit
+    for (int i = tid; i < ncut; i += LNT) {
+        const uint32_t k = s_key[i];
+        if ((k & KEY_DEAD) || !(k & (KEY_LTOP | KEY_RCAND))) continue;
+        const uint32_t mine = k & KEY_STATE;
+        int total = s_np[i], hops = 0;
+        bool first = true;
+        for (int j = s_succ[i]; j != i; j = s_succ[j]) {
+            const uint32_t kj = s_key[j];
+            if ((kj & (KEY_LTOP | KEY_RCAND)) && (kj & KEY_STATE) < mine) { first = false; break; }
+            total += s_np[j];
+            if (++hops > ncut) { s_bad = 1; first = false; break; }
+        }
+        if (!first) continue;
+        const int n = atomicAdd(&s_nstart, 1);
+        if (n >= MAXB) continue;
+        const int pos = (int)(mine >> 3), y = pos / W, x = pos - y * W;
+        const bool hole = k & KEY_RCAND;
+        s_start[n] = (short)i;
+        a.ukey[bbase + n] = ((uint32_t)(y * (W + 1) + x + (hole ? 1 : 0)) << 1) | (hole ? 1u : 0u);
+        a.unp[bbase + n] = total;
+        a.usteps[bbase + n] = total;
+    }
+    __syncthreads();
+    if (s_bad) { if (tid == 0) meta->fallback = 1; return; }
+    const int nstart = s_nstart;
+    if (nstart > MAXB) {
+        if (tid == 0) { meta->nstart = nstart; meta->flags |= FRAME_FLAG_BORDER_OVERFLOW; }
+        return;
+    }
+    if (tid == 0) meta->nstart = nstart;
+    rank_frame(a, frame, u.r, nstart, s_rank);
+    if (meta->flags) return;
+    for (int n = tid; n < nstart; n += LNT) {
+        const int b = s_rank[n], i0 = s_start[n];
+        int run = a.off[bbase + b], j = i0;
+        do {
+            a.cut_dst[base + j] = ((uint32_t)run << 10) | (uint32_t)b;
+            run += s_np[j];
+            j = s_succ[j];
+        } while (j != i0);
+    }
+}
+
+__global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
+{
+    __shared__ uint32_t s_tab[TABN];
+    const int frame = blockIdx.x, W = a.W;
+    const QMeta* meta = a.meta + frame;
+    if (meta->fallback || meta->flags || meta->nb == 0) return;
+    const int ncut = meta->ncut;
+    const size_t base = (size_t)frame * MAXCUT;
+    CutSet cs{s_tab, W};
+    for (int i = threadIdx.x; i < TABN; i += CNT) s_tab[i] = EMPTY;
+    __syncthreads();
+    for (int i = threadIdx.x; i < ncut; i += CNT) {
+        const uint32_t key = a.cut_key[base + i];
+        if (key & KEY_DEAD) continue;
+        if (key & KEY_LTOP) cs.insert(((key & KEY_STATE) >> 3) << 1);
+        if (key & KEY_RCAND) cs.insert((((key & KEY_STATE) >> 3) << 1) | 1u);
+    }
+    const PadImg im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
+    for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
+        const uint32_t d = a.cut_dst[base + slot];
+        if (d == EMPTY) continue;
+        const uint32_t key = a.cut_key[base + slot];
+        const int pos = (int)((key & KEY_STATE) >> 3), y = pos / W, x = pos - y * W;
+        const uint32_t nb = im.nbr(x, y);
+        SegEmit v{a.pts + (size_t)frame * MANTIS_MAX_PTS + (d >> 10), a.owner + (size_t)frame * W * a.H, W, (uint16_t)(d & 1023u)};
+        if (nb == 0u) { v.visit(x, y, 0xffu); v.point(x, y); continue; }
+        walk_piece(im, cs, x, y, (int)(key & 7u), nb, v);
+    }
+}
+
 // long contours: approxPolyDP by a whole warp
 constexpr int LWARPS = 4;
 __global__ void __launch_bounds__(32 * LWARPS) k_qapprox_long(QuadArgs a)
@@ -627,7 +971,7 @@ __global__ void __launch_bounds__(32 * LWARPS) k_qapprox_long(QuadArgs a)
     const int frame = blockIdx.x, lane = threadIdx.x & 31;
     const QMeta* meta = a.meta + frame;
     const int nlong = min(meta->nlong, MAXLONG);
-    if (meta->flags || nlong == 0) return;
+    if (meta->flags) return;
     const size_t base = (size_t)frame * MAXB;
     for (int k = threadIdx.x >> 5; k < nlong; k += LWARPS) {
         const int b = a.longl[(size_t)frame * MAXLONG + k];
@@ -642,6 +986,19 @@ __global__ void __launch_bounds__(32 * LWARPS) k_qapprox_long(QuadArgs a)
                 for (int q = 0; q < 4; ++q) a.quad[(base + b) * 4 + q] = dst[q];
         }
         __syncwarp();
+    }
+    if (!a.use_cuts || meta->fallback) return;  // the sequential route approximates short borders while tracing
+    const int nb = meta->nb;
+    for (int slot = threadIdx.x; slot < nb; slot += 32 * LWARPS) {
+        const int b = a.bylen[base + slot];
+        const int off = a.off[base + b], np = a.np[base + b];
+        if (np > LONG_NP) continue;
+        short2* dst = a.dst + (size_t)frame * MANTIS_MAX_PTS + off;
+        const int n4 = approx_poly_closed(a.pts + (size_t)frame * MANTIS_MAX_PTS + off, np, a.eps, dst,
+                                          a.stack + (size_t)frame * (MANTIS_MAX_PTS + 2 * MAXB) + off + 2 * b);
+        a.an[base + b] = (short)min(n4, 32767);
+        if (n4 == 4)
+            for (int q = 0; q < 4; ++q) a.quad[(base + b) * 4 + q] = dst[q];
     }
 }
 
@@ -794,7 +1151,9 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
     const size_t o_meta = take((size_t)n * sizeof(QMeta)), o_cand = take((size_t)n * MAXCAND * 4), o_ukey = take(nB * 4),
                  o_unp = take(nB * 4), o_ust = take(nB * 4), o_key = take(nB * 4), o_np = take(nB * 4), o_off = take(nB * 4),
-                 o_bylen = take(nB * 2), o_long = take((size_t)n * MAXLONG * 2), o_an = take(nB * 2), o_quad = take(nB * 4 * sizeof(short2));
+                 o_bylen = take(nB * 2), o_long = take((size_t)n * MAXLONG * 2), o_an = take(nB * 2), o_quad = take(nB * 4 * sizeof(short2)),
+                 o_cut = take((size_t)n * MAXCUT * 4), o_cend = take((size_t)n * MAXCUT * 4), o_cnp = take((size_t)n * MAXCUT * 4),
+                 o_cdst = take((size_t)n * MAXCUT * 4), o_ckey = take((size_t)n * MAXCUT * 4);
     if ((rc = ctx_reserve(c, c->q_stack, o)) ||
         (rc = ctx_reserve(c, c->q_pts, (size_t)n * MANTIS_MAX_PTS * sizeof(short2) * 2)) ||
         (rc = ctx_reserve(c, c->q_dst, (size_t)n * (MANTIS_MAX_PTS + 2 * MAXB) * sizeof(int2))) ||
@@ -808,6 +1167,8 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     a.unp = (int*)(ar + o_unp); a.usteps = (int*)(ar + o_ust); a.key = (uint32_t*)(ar + o_key);
     a.np = (int*)(ar + o_np); a.off = (int*)(ar + o_off); a.bylen = (short*)(ar + o_bylen); a.longl = (short*)(ar + o_long);
     a.an = (short*)(ar + o_an); a.quad = (short2*)(ar + o_quad);
+    a.cut = (uint32_t*)(ar + o_cut); a.cut_end = (uint32_t*)(ar + o_cend); a.cut_np = (int*)(ar + o_cnp); a.cut_dst = (uint32_t*)(ar + o_cdst);
+    a.cut_key = (uint32_t*)(ar + o_ckey);
     a.pts = (short2*)c->q_pts.p;
     a.dst = a.pts + (size_t)n * MANTIS_MAX_PTS;
     a.stack = (int2*)c->q_dst.p;
@@ -817,20 +1178,41 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     a.stretch = c->cfg.quad_stretch_factor;
     a.radius_mult = c->cfg.search_radius_multiplier;
     MCHECK(c, cudaMemsetAsync(a.meta, 0, (size_t)n * sizeof(QMeta), c->stream));
-    const int words = h * a.WW;
-    k_qcand<<<dim3((words + CNT - 1) / CNT, n), CNT, 0, c->stream>>>(a);
     const size_t plane = (size_t)(h + 2) * (a.WW + 2) * sizeof(uint32_t);
     const int use_smem = plane <= 200 * 1024;
+    a.use_cuts = use_smem && (size_t)w * h < (1u << 21) && !getenv("MANTIS_QUADS_SEQUENTIAL");  // (the variable is for tests)
     if (use_smem) {
         MCHECK(c, cudaFuncSetAttribute(k_qprobe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
         MCHECK(c, cudaFuncSetAttribute(k_qtrace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
+        MCHECK(c, cudaFuncSetAttribute(k_qseg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
+        MCHECK(c, cudaFuncSetAttribute(k_qemit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
     }
+    if (a.use_cuts) {
+        k_qcut<<<dim3(4, n), CNT, 0, c->stream>>>(a);
+        k_qseg<<<n, CNT, plane, c->stream>>>(a);
+        k_qlink<<<n, LNT, 0, c->stream>>>(a);
+        c->launches += 3;
+    }
+    // the sequential route: all frames when the plane does not fit in shared memory, else only the frames flagged above
+    k_qcand<<<dim3(a.use_cuts ? 2 : 16, n), CNT, 0, c->stream>>>(a);
     k_qprobe<<<n, CNT, use_smem ? plane : 0, c->stream>>>(a, use_smem);
     k_qrank<<<n, CNT, 0, c->stream>>>(a);
     k_qtrace<<<n, TNT, use_smem ? plane : 0, c->stream>>>(a, use_smem);
+    if (a.use_cuts) {
+        k_qemit<<<n, CNT, plane, c->stream>>>(a);
+        c->launches += 1;
+    }
     k_qapprox_long<<<n, 32 * LWARPS, 0, c->stream>>>(a);
     k_qfinish<<<n, FNT, 0, c->stream>>>(a);
     c->launches += 6;
     MCHECK(c, cudaGetLastError());
+    if (getenv("MANTIS_QUAD_DEBUG")) {  // how many frames took which route
+        std::vector<QMeta> hm(n);
+        MCHECK(c, cudaMemcpyAsync(hm.data(), a.meta, (size_t)n * sizeof(QMeta), cudaMemcpyDeviceToHost, c->stream));
+        MCHECK(c, cudaStreamSynchronize(c->stream));
+        long long fb = 0, cuts = 0, maxc = 0;
+        for (const QMeta& m : hm) { fb += m.fallback != 0; cuts += m.ncut; maxc = m.ncut > maxc ? m.ncut : maxc; }
+        fprintf(stderr, "quads: %d frames, %lld sequential, cuts mean %.1f max %lld\n", n, fb, (double)cuts / (n ? n : 1), maxc);
+    }
     return MANTIS_OK;
 }

@@ -80,3 +80,49 @@ def test_device_renderer_matches_oracle(ctx):
         diff = (got[i] != ref).any(axis=2).mean()
         assert diff < 1e-4, diff
         assert (ref > 200).any()
+
+
+def _blob_images(n, h, w, seed):
+    """Smoothed-noise blobs at several scales: nested holes, spirals of thin walls, frame contacts."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(n):
+        f = rng.random((h, w))
+        k = 2 + i % 7
+        for _ in range(2):  # box blur by cumulative sums
+            c = np.cumsum(np.pad(f, ((k, k), (0, 0)), mode="wrap"), axis=0)
+            f = c[2 * k:] - c[:-2 * k]
+            c = np.cumsum(np.pad(f, ((0, 0), (k, k)), mode="wrap"), axis=1)
+            f = c[:, 2 * k:] - c[:, :-2 * k]
+        f = (f - f.min()) / (np.ptp(f) + 1e-12)
+        g = (np.floor(f * (3 + i % 3)) % 2 * 255).astype(np.uint8)
+        out.append(np.repeat(g[:, :, None], 3, axis=2))
+    return np.stack(out)
+
+
+def test_quads_random_blobs_match_oracle(ctx):
+    frames = _blob_images(40, 150, 210, seed=5)
+    K, D = K_for(210, 150), np.zeros(4)
+    out = ctx.quads(frames)
+    contours = 0
+    for i in range(len(frames)):
+        tr, _ = po.localize(frames[i], K, D)
+        check_quads(out[i], tr)
+        contours += tr.n_contours
+    assert contours > 400
+
+
+def test_quad_routes_agree(ctx, monkeypatch):
+    """The piece-parallel tracer and the sequential-walk kernels it falls back to give the same frames."""
+    K, D = K_for(640, 480), np.zeros(4)
+    frames = np.stack([po.render_grid(R, t, K, D, 640, 480) for R, t in poses(6, seed=91)])
+    rng = np.random.default_rng(2)
+    frames[3] = np.clip(frames[3].astype(np.int16) + rng.integers(-60, 60, frames[3].shape), 0, 255).astype(np.uint8)
+    a = ctx.quads(frames)
+    monkeypatch.setenv("MANTIS_QUADS_SEQUENTIAL", "1")
+    b = ctx.quads(frames)
+    for fa, fb in zip(a, b):
+        assert (fa.flags, fa.n_contours, fa.n_quads_raw, fa.n_quads) == (fb.flags, fb.n_contours, fb.n_quads_raw, fb.n_quads)
+        for i in range(fa.n_quads):
+            assert list(fa.corners[i]) == list(fb.corners[i])
+            assert list(fa.test_px[i]) == list(fb.test_px[i])
