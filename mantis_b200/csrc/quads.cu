@@ -88,6 +88,10 @@ struct PadImg {
         // up: NW N NE, mid: W . E, dn: SW S SE  ->  direction order E NE N NW W SW S SE
         return (mid >> 2) | ((up & 4u) >> 1) | ((up & 2u) << 1) | ((up & 1u) << 3) | ((mid & 1u) << 4) | (dn << 5);
     }
+    __device__ __forceinline__ uint32_t at(int x, int y) const  // x in [-32, W + 31], y in [-1, H]
+    {
+        return (base[(y + 1) * stride + ((x + 32) >> 5)] >> ((x + 32) & 31)) & 1u;
+    }
 };
 
 __device__ __forceinline__ int dir_dx(int s) { return (int)((0x901Au >> (2 * s)) & 3u) - 1; }
@@ -404,6 +408,8 @@ struct QuadArgs {
     uint32_t* cut_key;    // [n][MAXCUT] visit keys (pixel << 3 | back direction) + KEY_ flags, from k_qseg
     uint32_t* cut_end;    // [n][MAXCUT] state at which the piece starting here ends
     int* cut_np;          // [n][MAXCUT] CHAIN_APPROX_SIMPLE vertices of the piece
+    uint32_t* cut_par;    // [n][MAXCUT] hole candidates: a cut visit of the border that owns the left edge of the run left of the hole
+    short* hole_owner;    // [n][MAXB] that border, for the hole borders
     uint32_t* cut_dst;    // [n][MAXCUT] (offset of the piece's vertices in its frame << 10) | border
     int use_cuts;
     FrameQuads* out;
@@ -744,13 +750,7 @@ struct SegCount {
 };
 struct SegEmit {
     short2* out;
-    uint16_t* owner;
-    int W;
-    uint16_t id;
-    __device__ __forceinline__ void visit(int x, int y, uint32_t z)
-    {
-        if (z & 0x10u) owner[(size_t)y * W + x] = id;  // this border owns the left edge of (x, y)
-    }
+    __device__ __forceinline__ void visit(int, int, uint32_t) {}
     __device__ __forceinline__ void point(int x, int y) { *out++ = make_short2((short)x, (short)y); }
 };
 
@@ -832,6 +832,20 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
                 np = v.np;
             }
         }
+        if (key & KEY_RCAND) {
+            // RETR_CCOMP parent of the hole that would start here: the border passing the left edge of
+            // the foreground run that ends at this pixel.  Any cut visit of that border identifies it:
+            // the visit examining that left edge, or the first cut after it.
+            int xl = x;
+            while (im.at(xl - 1, y)) --xl;
+            const uint32_t nbl = im.nbr(xl, y);  // not empty: the run's right end has a neighbour above
+            const int sl = back_dir(nbl, 4), r0 = (sl + 1) & 7;
+            const uint32_t rot = ((nbl | (nbl << 8)) >> r0) & 0xffu;
+            uint32_t z = ((1u << (__ffs(rot) - 1)) - 1u) << r0;
+            z = (z | (z >> 8)) & 0xffu;
+            SegCount v{0};
+            a.cut_par[base + slot] = cs.is_cut(xl, y, nbl, z) ? (((uint32_t)(y * W + xl) << 3) | (uint32_t)sl) : walk_piece(im, cs, xl, y, sl, nbl, v);
+        }
         if (np > 65535) meta->fallback = 1;
         a.cut_key[base + slot] = key;
         a.cut_end[base + slot] = end;
@@ -844,7 +858,7 @@ __global__ void __launch_bounds__(LNT) k_qlink(QuadArgs a)
 {
     __shared__ uint32_t s_key[MAXCUT];
     __shared__ uint16_t s_succ[MAXCUT], s_np[MAXCUT];
-    __shared__ short s_start[MAXB], s_rank[MAXB];
+    __shared__ short s_start[MAXB], s_rank[MAXB], s_par[MAXB];
     __shared__ union U {
         struct { uint32_t key[HASHN]; uint16_t val[HASHN]; } h;
         RankSmem r;
@@ -909,6 +923,16 @@ __global__ void __launch_bounds__(LNT) k_qlink(QuadArgs a)
         const int pos = (int)(mine >> 3), y = pos / W, x = pos - y * W;
         const bool hole = k & KEY_RCAND;
         s_start[n] = (short)i;
+        if (hole) {  // a piece of the border that owns the hole (its parent in RETR_CCOMP, or a hole beside it)
+            const uint32_t st = a.cut_par[base + i];
+            uint32_t h = slot_of(st);
+            for (;; h = (h + 1) & (HASHN - 1)) {
+                const uint32_t kk = u.h.key[h];
+                if (kk == st || kk == EMPTY) break;
+            }
+            if (u.h.key[h] == st) s_par[n] = (short)u.h.val[h];
+            else s_bad = 1;
+        }
         a.ukey[bbase + n] = ((uint32_t)(y * (W + 1) + x + (hole ? 1 : 0)) << 1) | (hole ? 1u : 0u);
         a.unp[bbase + n] = total;
         a.usteps[bbase + n] = total;
@@ -932,6 +956,9 @@ __global__ void __launch_bounds__(LNT) k_qlink(QuadArgs a)
             j = s_succ[j];
         } while (j != i0);
     }
+    __syncthreads();
+    for (int n = tid; n < nstart; n += LNT)
+        if (s_key[s_start[n]] & KEY_RCAND) a.hole_owner[bbase + s_rank[n]] = (short)(a.cut_dst[base + s_par[n]] & 1023u);
 }
 
 __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
@@ -958,8 +985,8 @@ __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
         const uint32_t key = a.cut_key[base + slot];
         const int pos = (int)((key & KEY_STATE) >> 3), y = pos / W, x = pos - y * W;
         const uint32_t nb = im.nbr(x, y);
-        SegEmit v{a.pts + (size_t)frame * MANTIS_MAX_PTS + (d >> 10), a.owner + (size_t)frame * W * a.H, W, (uint16_t)(d & 1023u)};
-        if (nb == 0u) { v.visit(x, y, 0xffu); v.point(x, y); continue; }
+        SegEmit v{a.pts + (size_t)frame * MANTIS_MAX_PTS + (d >> 10)};
+        if (nb == 0u) { v.point(x, y); continue; }
         walk_piece(im, cs, x, y, (int)(key & 7u), nb, v);
     }
 }
@@ -1033,8 +1060,14 @@ __global__ void __launch_bounds__(FNT) k_qfinish(QuadArgs a)
     for (int b = tid; b < nb; b += FNT) { s_key[b] = a.key[base + b]; s_an[b] = a.an[base + b]; }
     __syncthreads();
     // hole -> outer border of its component
+    const bool pieces = a.use_cuts && !meta->fallback;
     for (int b = tid; b < nb; b += FNT) {
         int cur = b;
+        if (pieces) {
+            while (s_key[cur] & 1u) cur = a.hole_owner[base + cur];
+            s_parent[b] = (short)cur;
+            continue;
+        }
         while (s_key[cur] & 1u) {  // climb: left end of the foreground run left of the hole start
             int p = (int)(s_key[cur] >> 1), y = p / (W + 1), x = p - y * (W + 1);
             int xl = x - 1;
@@ -1085,33 +1118,50 @@ __global__ void __launch_bounds__(FNT) k_qfinish(QuadArgs a)
         s_neighbor[e] = 0;
     }
     __syncthreads();
-    if (tid == 0) {
+    if (tid < 32) {
         // removeDuplicateQuads: exact radius search, 4 results, unfilled slots alias quad 0.
-        // Sequential over quads as in the reference (a quad marked by an earlier one is skipped).
+        // Sequential over quads as in the reference (a quad marked by an earlier one is skipped); the
+        // search of one quad is spread over the warp: every lane keeps (distance, index) keys of its
+        // quads and the four smallest are taken one after the other (ties: the smaller index, which
+        // is what the reference's stable insertion keeps).
+        constexpr int PER = MANTIS_MAX_QUADS / 32;
         for (int e = 0; e < nraw; ++e) {
-            if (s_neighbor[e]) continue;
+            if (s_neighbor[e]) continue;  // (uniform: read after the __syncwarp below)
             const short2* q = quad + 4 * s_qb[e];
             int ddx = q[0].x - q[1].x, ddy = q[0].y - q[1].y;
             double side = sqrt((double)(ddx * ddx + ddy * ddy));
             float radius = (float)(a.radius_mult * side);
-            int idx[4] = {0, 0, 0, 0};
-            float dd[4];
-            int found = 0;
-            for (int j = 0; j < nraw; ++j) {
-                float fx = s_cx[e] - s_cx[j], fy = s_cy[e] - s_cy[j];
-                float d = __fadd_rn(__fmul_rn(fx, fx), __fmul_rn(fy, fy));
-                if (!(d <= radius)) continue;
-                int pos = found < 4 ? found : 4;
-                while (pos > 0 && dd[pos - 1] > d) --pos;
-                if (pos >= 4) continue;
-                int last = found < 4 ? found : 3;
-                for (int k = last; k > pos; --k) { dd[k] = dd[k - 1]; idx[k] = idx[k - 1]; }
-                dd[pos] = d;
-                idx[pos] = j;
-                if (found < 4) ++found;
+            unsigned long long key[PER];
+#pragma unroll
+            for (int t = 0; t < PER; ++t) {
+                const int j = tid + 32 * t;
+                key[t] = ~0ull;
+                if (j < nraw) {
+                    float fx = s_cx[e] - s_cx[j], fy = s_cy[e] - s_cy[j];
+                    float d = __fadd_rn(__fmul_rn(fx, fx), __fmul_rn(fy, fy));
+                    if (d <= radius) key[t] = ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)j;
+                }
             }
-            for (int k = 1; k < 4; ++k) s_neighbor[idx[k]] = 1;
+            int found = 0;
+            for (; found < 4; ++found) {
+                unsigned long long m = key[0];
+#pragma unroll
+                for (int t = 1; t < PER; ++t) m = key[t] < m ? key[t] : m;
+                const unsigned dm = __reduce_min_sync(0xffffffffu, (unsigned)(m >> 32));
+                if (dm == 0xffffffffu) break;
+                const unsigned jm = __reduce_min_sync(0xffffffffu, (unsigned)(m >> 32) == dm ? (unsigned)m : 0xffffffffu);
+                const unsigned long long taken = ((unsigned long long)dm << 32) | jm;
+#pragma unroll
+                for (int t = 0; t < PER; ++t)
+                    if (key[t] == taken) key[t] = ~0ull;
+                if (found >= 1 && tid == 0) s_neighbor[jm] = 1;
+            }
+            if (found < 4 && tid == 0) s_neighbor[0] = 1;
+            __syncwarp();
         }
+    }
+    __syncthreads();
+    if (tid == 0) {
         int nq = 0;
         for (int e = 0; e < nraw; ++e) {
             short slot = -1;
@@ -1153,7 +1203,8 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
                  o_unp = take(nB * 4), o_ust = take(nB * 4), o_key = take(nB * 4), o_np = take(nB * 4), o_off = take(nB * 4),
                  o_bylen = take(nB * 2), o_long = take((size_t)n * MAXLONG * 2), o_an = take(nB * 2), o_quad = take(nB * 4 * sizeof(short2)),
                  o_cut = take((size_t)n * MAXCUT * 4), o_cend = take((size_t)n * MAXCUT * 4), o_cnp = take((size_t)n * MAXCUT * 4),
-                 o_cdst = take((size_t)n * MAXCUT * 4), o_ckey = take((size_t)n * MAXCUT * 4);
+                 o_cdst = take((size_t)n * MAXCUT * 4), o_ckey = take((size_t)n * MAXCUT * 4),
+                 o_cpar = take((size_t)n * MAXCUT * 4), o_hown = take(nB * 2);
     if ((rc = ctx_reserve(c, c->q_stack, o)) ||
         (rc = ctx_reserve(c, c->q_pts, (size_t)n * MANTIS_MAX_PTS * sizeof(short2) * 2)) ||
         (rc = ctx_reserve(c, c->q_dst, (size_t)n * (MANTIS_MAX_PTS + 2 * MAXB) * sizeof(int2))) ||
@@ -1168,7 +1219,7 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     a.np = (int*)(ar + o_np); a.off = (int*)(ar + o_off); a.bylen = (short*)(ar + o_bylen); a.longl = (short*)(ar + o_long);
     a.an = (short*)(ar + o_an); a.quad = (short2*)(ar + o_quad);
     a.cut = (uint32_t*)(ar + o_cut); a.cut_end = (uint32_t*)(ar + o_cend); a.cut_np = (int*)(ar + o_cnp); a.cut_dst = (uint32_t*)(ar + o_cdst);
-    a.cut_key = (uint32_t*)(ar + o_ckey);
+    a.cut_key = (uint32_t*)(ar + o_ckey); a.cut_par = (uint32_t*)(ar + o_cpar); a.hole_owner = (short*)(ar + o_hown);
     a.pts = (short2*)c->q_pts.p;
     a.dst = a.pts + (size_t)n * MANTIS_MAX_PTS;
     a.stack = (int2*)c->q_dst.p;
