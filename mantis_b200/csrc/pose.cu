@@ -44,6 +44,7 @@ struct PoseArgs {
     double* candR;           // [cap * 2 * 4][9]
     RunOut* run2;            // [cap * 2 * 4]
     int cap;
+    long long* dbg;          // tuning aid (null = off): slots 10..15 = AbsKernel steps spent in runs of <16, <64, <256, <1024, <4096, more steps
     double half_spacing, max_quad_error, cluster_radius;
     Tf rotz;                 // tf::Transform(tf::Quaternion(0, 0, 1/sqrt2, 1/sqrt2))
 };
@@ -79,13 +80,16 @@ __global__ void __launch_bounds__(PNT) k_pose_prep(PoseArgs a)
 // lanes pick up the next queued run every few trips, so lanes with short runs do not idle behind
 // long ones (runs take 2 .. several hundred steps).
 constexpr int RNT = 128;
+#ifndef RUN_CTAS
+#define RUN_CTAS 3
+#endif
 template <bool HAS_INIT>
-__global__ void __launch_bounds__(RNT) k_pose_run(PoseArgs a, int round)
+__global__ void __launch_bounds__(RNT, RUN_CTAS) k_pose_run(PoseArgs a, int round)
 {
-    __shared__ double s_ctx[rppf::CTX_WORDS][RNT];
+    extern __shared__ double s_ctx[];  // [rppf::CTX_WORDS][RNT]
     const double TOL = 1e-5, EPSILON = 1e-8;
     const int lane = threadIdx.x & 31;
-    double* ctx = &s_ctx[0][threadIdx.x];
+    double* ctx = s_ctx + threadIdx.x;
     const int* list = HAS_INIT ? a.list2 + (size_t)round * a.cap * 4 : a.list1 + (size_t)round * a.cap;
     const int ntask = HAS_INIT ? a.cnt->n_t2[round] : a.cnt->n_t1[round];
     int* fetch = HAS_INIT ? &a.cnt->fetch2[round] : &a.cnt->fetch1[round];
@@ -110,18 +114,13 @@ __global__ void __launch_bounds__(RNT) k_pose_run(PoseArgs a, int round)
                         const int entry = HAS_INIT ? (task >> 2) : task;
                         double m[8];
                         model_xy(a.half_spacing, entry & 1, m);
-                        rppf::setup(ctx, RNT, a.rays + (size_t)(entry >> 1) * 8, m);
+                        rppf::setup(ctx, RNT, a.rays + (size_t)(entry >> 1) * 8, m, L);
                         it = 0;
                         if (HAS_INIT) {
                             old_err = rppf::init_from_R(ctx, RNT, a.candR + (size_t)task * 9, L);
                             pending = 1;
                         } else {
-                            for (int i = 0; i < 4; ++i) {
-                                L.Q[i][0] = a.rays[(size_t)(entry >> 1) * 8 + 2 * i];
-                                L.Q[i][1] = a.rays[(size_t)(entry >> 1) * 8 + 2 * i + 1];
-                                L.Q[i][2] = 1.0;
-                            }
-                            pending = 2;
+                            pending = 2;  // the run starts from the rays themselves (setup)
                         }
                     } else {
                         exhausted = true;
@@ -140,11 +139,12 @@ __global__ void __launch_bounds__(RNT) k_pose_run(PoseArgs a, int round)
                 if (pending == 0) old_err = new_err;
                 new_err = e;
                 pending = 0;
-                stop = !(fabs((old_err - new_err) / old_err) > TOL && new_err > EPSILON) || ++it > 100000;
+                stop = !(fabs(old_err - new_err) > TOL * fabs(old_err) && new_err > EPSILON) || ++it > 100000;  // |(old - new) / old| > TOL without the division
             }
             if (stop) {
+                if (a.dbg && !HAS_INIT) atomicAdd((unsigned long long*)&a.dbg[10 + (it >= 16) + (it >= 64) + (it >= 256) + (it >= 1024) + (it >= 4096)], (unsigned long long)it);
                 RunOut o;
-                rppf::finalize(ctx, RNT, L, new_err, o.R, o.t, o.obj_err, o.img_err);
+                rppf::finalize(ctx, RNT, L, o.R, o.t, o.obj_err, o.img_err);
                 out[task] = o;
                 task = -1;
             }
@@ -364,14 +364,18 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
     a.cnt = (PoseCounters*)(ws + o_cnt); a.rays = (double*)(ws + o_rays); a.list1 = (int*)(ws + o_l1);
     a.list2 = (int*)(ws + o_l2); a.run1 = (RunOut*)(ws + o_run1); a.ncand = (int*)(ws + o_nc);
     a.candR = (double*)(ws + o_cr); a.run2 = (RunOut*)(ws + o_run2);
+    a.dbg = (long long*)c->dbg_clocks;
     MCHECK(c, cudaMemsetAsync(a.cnt, 0, sizeof(PoseCounters), c->stream));
     k_pose_prep<<<n, PNT, 0, c->stream>>>(a);
     static const int rb = []() { const char* e = getenv("MANTIS_RUN_BLOCKS"); int v = e ? atoi(e) : 0; return v > 0 ? v : 4; }();
     const int run_blocks = c->sm_count * rb, flat_blocks = c->sm_count * 4;
+    const int run_smem = rppf::CTX_WORDS * RNT * (int)sizeof(double);
+    MCHECK(c, cudaFuncSetAttribute(k_pose_run<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, run_smem));
+    MCHECK(c, cudaFuncSetAttribute(k_pose_run<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, run_smem));
     for (int round = 0; round < 2; ++round) {
-        k_pose_run<false><<<run_blocks, RNT, 0, c->stream>>>(a, round);
+        k_pose_run<false><<<run_blocks, RNT, run_smem, c->stream>>>(a, round);
         k_pose_second<<<flat_blocks, PNT, 0, c->stream>>>(a, round);
-        k_pose_run<true><<<run_blocks, RNT, 0, c->stream>>>(a, round);
+        k_pose_run<true><<<run_blocks, RNT, run_smem, c->stream>>>(a, round);
         k_pose_select<<<flat_blocks, PNT, 0, c->stream>>>(a, round);
     }
     k_pose_cluster<<<n, PNT, 0, c->stream>>>(a);

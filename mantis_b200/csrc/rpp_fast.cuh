@@ -9,8 +9,26 @@
 //     s = |a x b| = sqrt(det A^T A),  k = sqrt(trace + 2 s).
 // The reference's sign fix-ups (RPP.cpp:283-310) only act when the translation comes out behind
 // the camera; that case, and a numerically rank-deficient A, go through the general SVD step
-// (rpp::abs_kernel in rpp.cuh).  F_i x is evaluated as v_i (v_i . x) / (v_i . v_i).
+// (rpp::abs_kernel in rpp.cuh).
+//
+// Between two steps the points are Q_i = R P_i + t, so everything a step needs is linear or
+// quadratic in (r1, r2, t) with per-run constant matrices (F_i = v_i v_i^T / v_i.v_i, symmetric):
+//     a = sum px_i F_i Q_i = Gxx r1 + Gxy r2 + Gx t        Gxx = sum px_i^2 F_i, Gxy = sum px_i py_i F_i,
+//     b = sum py_i F_i Q_i = Gxy r1 + Gyy r2 + Gy t        Gx = sum px_i F_i, G1 = sum F_i, ...
+//     t = tF sum F_i R P_i = tF (Gx r1 + Gy r2)
+//     sum |Q_i - F_i Q_i|^2 = sum |Q_i|^2 - (r1.a + r2.b + t.(Gx r1 + Gy r2 + G1 t))     (I - F_i is a projector)
+// and, t being linear in (r1, r2) and (r1, r2) linear in (a, b) once the three polar coefficients c
+// are known,
+//     a' = c11 Kxx a + c12 (Kxx b + Kxy a) + c22 Kxy b      Kxx = Gxx + Gx tF Gx,  Kxy = Gxy + Gx tF Gy,
+//     b' = c11 Kxy^T a + c12 (Kxy^T b + Kyy a) + c22 Kyy b  Kyy = Gyy + Gy tF Gy.
+// A run is a chain of dependent steps and the longest runs (thousands of steps) set the duration of
+// the whole launch, so what matters is the LATENCY of a step: all matrix-vector products above
+// depend only on (a, b) and issue beside the scalar chain (a, b) -> c, after which a', b' are three
+// multiply-adds away.  R, t and the error hang off that chain.  The state of a run is (a, b, r1, r2, t).  The error used by the stopping rule carries the cancellation of that
+// difference (~1e-14 absolute, against errors of 1e-8 and up and a relative tolerance of 1e-5);
+// the error reported at the end is recomputed point by point.
 #pragma once
+#include "fastmath.cuh"
 #include "rpp.cuh"
 
 namespace rppf {
@@ -18,74 +36,179 @@ namespace rppf {
 constexpr int NPT = 4;
 
 // Read-only data of one run, kept in shared memory column `lane` of a [CTX_WORDS][threads] array.
-enum { C_VX = 0, C_VY = 4, C_IVV = 8, C_PX = 12, C_PY = 16, C_TF = 20, C_PBX = 29, C_PBY = 30, CTX_WORDS = 31 };
+// Symmetric matrices are stored as xx xy xz yy yz zz.
+// Kxy is general (row-major, 9 words).
+enum {
+    C_VX = 0, C_VY = 4, C_PX = 8, C_PY = 12, C_KXX = 16, C_KXY = 22, C_KYY = 31, C_GX = 37, C_GY = 43, C_G1 = 49, C_TF = 55,
+    C_CXX = 61, C_CXY = 62, C_CYY = 63, C_PBX = 64, C_PBY = 65, CTX_WORDS = 66
+};
 
 struct Lane {            // registers of one run
-    double Q[NPT][3];
-    double r1[3], r2[3], r3[3], t[3];
+    double a[3], b[3];   // sum px_i F_i Q_i, sum py_i F_i Q_i for the current points
+    double r1[3], r2[3], t[3];
+    bool rays;           // the current points are still the image rays (first step of a run without initial R)
 };
 
 #define RPPF_C(k) ctx[(k) * stride]
 
-// rays (x, y, 1) and model (x, y, 0) -> context.  Mirrors rpp::setup.
-__device__ inline void setup(double* ctx, int stride, const double* ray_xy, const double* model_xy)
+// out = G x for the symmetric matrix at context word g
+__device__ __forceinline__ void symv(const double* ctx, int stride, int g, const double* x, double* out)
+{
+    const double xx = RPPF_C(g), xy = RPPF_C(g + 1), xz = RPPF_C(g + 2), yy = RPPF_C(g + 3), yz = RPPF_C(g + 4), zz = RPPF_C(g + 5);
+    out[0] = fma(xz, x[2], fma(xy, x[1], xx * x[0]));
+    out[1] = fma(yz, x[2], fma(yy, x[1], xy * x[0]));
+    out[2] = fma(zz, x[2], fma(yz, x[1], xz * x[0]));
+}
+__device__ __forceinline__ void symv_acc(const double* ctx, int stride, int g, const double* x, double* out)
+{
+    const double xx = RPPF_C(g), xy = RPPF_C(g + 1), xz = RPPF_C(g + 2), yy = RPPF_C(g + 3), yz = RPPF_C(g + 4), zz = RPPF_C(g + 5);
+    out[0] = fma(xz, x[2], fma(xy, x[1], fma(xx, x[0], out[0])));
+    out[1] = fma(yz, x[2], fma(yy, x[1], fma(xy, x[0], out[1])));
+    out[2] = fma(zz, x[2], fma(yz, x[1], fma(xz, x[0], out[2])));
+}
+
+// out = K x and out_t = K^T y for the general matrix at context word g
+__device__ __forceinline__ void genv2(const double* ctx, int stride, int g, const double* x, const double* y, double* out, double* out_t)
+{
+    double k[9];
+    for (int i = 0; i < 9; ++i) k[i] = RPPF_C(g + i);
+    for (int r = 0; r < 3; ++r) {
+        out[r] = fma(k[3 * r + 2], x[2], fma(k[3 * r + 1], x[1], k[3 * r] * x[0]));
+        out_t[r] = fma(k[6 + r], y[2], fma(k[3 + r], y[1], k[r] * y[0]));
+    }
+}
+
+// rays (x, y, 1) and model (x, y, 0) -> context; the run starts from Q_i = v_i.  Mirrors rpp::setup.
+__device__ inline void setup(double* ctx, int stride, const double* ray_xy, const double* model_xy, Lane& L)
 {
     double pbx = 0, pby = 0;
     for (int i = 0; i < NPT; ++i) { pbx += model_xy[2 * i]; pby += model_xy[2 * i + 1]; }
     pbx /= NPT; pby /= NPT;
-    pm::M3 sumF;
-    for (int k = 0; k < 9; ++k) sumF.m[k] = 0;
+    double gxx[6], gxy[6], gyy[6], gx[6], gy[6], g1[6], cxx = 0, cxy = 0, cyy = 0;
+    for (int k = 0; k < 6; ++k) gxx[k] = gxy[k] = gyy[k] = gx[k] = gy[k] = g1[k] = 0;
+    for (int k = 0; k < 3; ++k) L.a[k] = L.b[k] = L.r1[k] = L.r2[k] = L.t[k] = 0;
     for (int i = 0; i < NPT; ++i) {
         const double v[3] = {ray_xy[2 * i], ray_xy[2 * i + 1], 1.0};
         const double vv = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+        const double px = model_xy[2 * i] - pbx, py = model_xy[2 * i + 1] - pby;
         RPPF_C(C_VX + i) = v[0];
         RPPF_C(C_VY + i) = v[1];
-        RPPF_C(C_IVV + i) = 1.0 / vv;
-        RPPF_C(C_PX + i) = model_xy[2 * i] - pbx;
-        RPPF_C(C_PY + i) = model_xy[2 * i + 1] - pby;
-        for (int a = 0; a < 3; ++a)
-            for (int b = 0; b < 3; ++b) sumF.m[a * 3 + b] += (v[a] * v[b]) / vv;
+        RPPF_C(C_PX + i) = px;
+        RPPF_C(C_PY + i) = py;
+        const double f[6] = {(v[0] * v[0]) / vv, (v[0] * v[1]) / vv, (v[0] * v[2]) / vv, (v[1] * v[1]) / vv, (v[1] * v[2]) / vv, (v[2] * v[2]) / vv};
+        for (int k = 0; k < 6; ++k) {
+            g1[k] += f[k];
+            gx[k] += px * f[k];
+            gy[k] += py * f[k];
+            gxx[k] += px * px * f[k];
+            gxy[k] += px * py * f[k];
+            gyy[k] += py * py * f[k];
+        }
+        cxx += px * px; cxy += px * py; cyy += py * py;
+        for (int k = 0; k < 3; ++k) { L.a[k] += px * v[k]; L.b[k] += py * v[k]; }  // F_i v_i = v_i
     }
+    L.rays = true;
     pm::M3 A = pm::eye();
-    for (int k = 0; k < 9; ++k) A.m[k] -= sumF.m[k] / NPT;
+    const int full[9] = {0, 1, 2, 1, 3, 4, 2, 4, 5};
+    for (int k = 0; k < 9; ++k) A.m[k] -= g1[full[k]] / NPT;
     pm::M3 tF = pm::inverse(A);
-    for (int k = 0; k < 9; ++k) RPPF_C(C_TF + k) = tF.m[k] / NPT;
+    const int upper[6] = {0, 1, 2, 4, 5, 8};
+    double tf[9], GX[9], GY[9], TX[9], TY[9];   // tF, Gx, Gy, tF Gx, tF Gy as full matrices
+    for (int k = 0; k < 9; ++k) { tf[k] = tF.m[upper[full[k]]] / NPT; GX[k] = gx[full[k]]; GY[k] = gy[full[k]]; }
+    for (int r = 0; r < 3; ++r)
+        for (int cc = 0; cc < 3; ++cc) {
+            TX[3 * r + cc] = tf[3 * r] * GX[cc] + tf[3 * r + 1] * GX[3 + cc] + tf[3 * r + 2] * GX[6 + cc];
+            TY[3 * r + cc] = tf[3 * r] * GY[cc] + tf[3 * r + 1] * GY[3 + cc] + tf[3 * r + 2] * GY[6 + cc];
+        }
+    for (int r = 0; r < 3; ++r)
+        for (int cc = 0; cc < 3; ++cc) {
+            const double xx = GX[3 * r] * TX[cc] + GX[3 * r + 1] * TX[3 + cc] + GX[3 * r + 2] * TX[6 + cc];
+            const double xy = GX[3 * r] * TY[cc] + GX[3 * r + 1] * TY[3 + cc] + GX[3 * r + 2] * TY[6 + cc];
+            const double yy = GY[3 * r] * TY[cc] + GY[3 * r + 1] * TY[3 + cc] + GY[3 * r + 2] * TY[6 + cc];
+            RPPF_C(C_KXY + 3 * r + cc) = gxy[full[3 * r + cc]] + xy;
+            if (cc >= r) {
+                const int u = r == 0 ? cc : (r == 1 ? 2 + cc : 5);
+                RPPF_C(C_KXX + u) = gxx[u] + xx;
+                RPPF_C(C_KYY + u) = gyy[u] + yy;
+            }
+        }
+    for (int k = 0; k < 6; ++k) {
+        RPPF_C(C_TF + k) = tF.m[upper[k]] / NPT;
+        RPPF_C(C_GX + k) = gx[k]; RPPF_C(C_GY + k) = gy[k]; RPPF_C(C_G1 + k) = g1[k];
+    }
+    RPPF_C(C_CXX) = cxx; RPPF_C(C_CXY) = cxy; RPPF_C(C_CYY) = cyy;
     RPPF_C(C_PBX) = pbx;
     RPPF_C(C_PBY) = pby;
 }
 
-// F_i x
-__device__ __forceinline__ void apply_F(const double* ctx, int stride, int i, const double* x, double* out)
+// The current points of the run: the rays, or R P_i + t.
+__device__ __forceinline__ void point(const double* ctx, int stride, const Lane& L, int i, double* q)
 {
-    const double vx = RPPF_C(C_VX + i), vy = RPPF_C(C_VY + i);
-    const double w = (vx * x[0] + vy * x[1] + x[2]) * RPPF_C(C_IVV + i);
-    out[0] = vx * w; out[1] = vy * w; out[2] = w;
+    if (L.rays) { q[0] = RPPF_C(C_VX + i); q[1] = RPPF_C(C_VY + i); q[2] = 1.0; return; }
+    const double px = RPPF_C(C_PX + i), py = RPPF_C(C_PY + i);
+    for (int k = 0; k < 3; ++k) q[k] = (L.r1[k] * px + L.r2[k] * py) + L.t[k];
 }
 
-__device__ __forceinline__ void mul_tF(const double* ctx, int stride, const double* s, double* t)
-{
-    for (int r = 0; r < 3; ++r)
-        t[r] = RPPF_C(C_TF + 3 * r) * s[0] + RPPF_C(C_TF + 3 * r + 1) * s[1] + RPPF_C(C_TF + 3 * r + 2) * s[2];
-}
-
-// Q_i = R P_i + t; returns sum |Q_i - F_i Q_i|^2
-__device__ __forceinline__ double reproject(const double* ctx, int stride, Lane& L)
+// sum |Q_i - F_i Q_i|^2 point by point, as the reference accumulates it
+__device__ inline double point_error(const double* ctx, int stride, const Lane& L)
 {
     double err2 = 0;
     for (int i = 0; i < NPT; ++i) {
-        const double px = RPPF_C(C_PX + i), py = RPPF_C(C_PY + i);
-        double q[3], fq[3];
-        for (int k = 0; k < 3; ++k) q[k] = (L.r1[k] * px + L.r2[k] * py) + L.t[k];
-        apply_F(ctx, stride, i, q, fq);
-        for (int k = 0; k < 3; ++k) { L.Q[i][k] = q[k]; double e = q[k] - fq[k]; err2 += e * e; }
+        double q[3];
+        point(ctx, stride, L, i, q);
+        const double vx = RPPF_C(C_VX + i), vy = RPPF_C(C_VY + i);
+        const double w = (vx * q[0] + vy * q[1] + q[2]) / (vx * vx + vy * vy + 1.0);
+        const double e0 = q[0] - vx * w, e1 = q[1] - vy * w, e2 = q[2] - w;
+        err2 += e0 * e0 + e1 * e1 + e2 * e2;
     }
     return err2;
 }
 
+// sum |Q_i|^2 - sum Q_i.F_i Q_i for Q_i = R P_i + t, given a = sum px_i F_i Q_i, b = sum py_i F_i Q_i and
+// gs = Gx r1 + Gy r2
+__device__ __forceinline__ double quad_error(const double* ctx, int stride, const double* r1, const double* r2, const double* t,
+                                             const double* a, const double* b, const double* gs)
+{
+    double g[3];
+    symv(ctx, stride, C_G1, t, g);
+    double qfq = 0, r11 = 0, r12 = 0, r22 = 0, tt = 0;
+    for (int k = 0; k < 3; ++k) {
+        qfq = fma(r1[k], a[k], fma(r2[k], b[k], fma(t[k], gs[k] + g[k], qfq)));
+        r11 = fma(r1[k], r1[k], r11); r12 = fma(r1[k], r2[k], r12); r22 = fma(r2[k], r2[k], r22); tt = fma(t[k], t[k], tt);
+    }
+    const double qq = fma(RPPF_C(C_CXX), r11, fma(2.0 * RPPF_C(C_CXY), r12, fma(RPPF_C(C_CYY), r22, NPT * tt)));
+    return qq - qfq;
+}
+
+// With (r1, r2) set and t = tF (Gx r1 + Gy r2): t, a, b of the new points and their error.
+__device__ inline double refresh(const double* ctx, int stride, Lane& L)
+{
+    double gs[3], ta[3], tb[3];
+    symv(ctx, stride, C_GX, L.r1, gs);
+    symv_acc(ctx, stride, C_GY, L.r2, gs);
+    symv(ctx, stride, C_TF, gs, L.t);
+    symv(ctx, stride, C_KXX, L.r1, L.a);
+    symv(ctx, stride, C_KYY, L.r2, L.b);
+    genv2(ctx, stride, C_KXY, L.r2, L.r1, ta, tb);
+    for (int k = 0; k < 3; ++k) { L.a[k] += ta[k]; L.b[k] += tb[k]; }
+    L.rays = false;
+    return quad_error(ctx, stride, L.r1, L.r2, L.t, L.a, L.b, gs);
+}
+
 // The general step through the 3x3 SVD (rare): rebuilds the reference-shaped context.
-__device__ __noinline__ double abs_kernel_general(const double* ctx, int stride, Lane& L)
+__device__ __noinline__ double abs_kernel_general_impl(const double* ctx, int stride, Lane& L);
+// (through a copy, so that the caller's Lane never has its address taken and stays in registers)
+__device__ __forceinline__ double abs_kernel_general(const double* ctx, int stride, Lane& L)
+{
+    Lane tmp = L;
+    const double e = abs_kernel_general_impl(ctx, stride, tmp);
+    L = tmp;
+    return e;
+}
+__device__ __noinline__ double abs_kernel_general_impl(const double* ctx, int stride, Lane& L)
 {
     rpp::ObjCtx<NPT> c;
+    pm::V3 Q[NPT];
     for (int i = 0; i < NPT; ++i) {
         const double v[3] = {RPPF_C(C_VX + i), RPPF_C(C_VY + i), 1.0};
         const double vv = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
@@ -94,87 +217,82 @@ __device__ __noinline__ double abs_kernel_general(const double* ctx, int stride,
             c.Qp[i].v[a] = v[a];
             for (int b = 0; b < 3; ++b) c.F[i].m[a * 3 + b] = (v[a] * v[b]) / vv;
         }
+        point(ctx, stride, L, i, Q[i].v);
     }
-    for (int k = 0; k < 9; ++k) c.tF.m[k] = RPPF_C(C_TF + k);
+    const int full[9] = {0, 1, 2, 1, 3, 4, 2, 4, 5};
+    for (int k = 0; k < 9; ++k) c.tF.m[k] = RPPF_C(C_TF + full[k]);
     c.pbar.v[0] = RPPF_C(C_PBX); c.pbar.v[1] = RPPF_C(C_PBY); c.pbar.v[2] = 0;
-    pm::V3 Q[NPT];
-    for (int i = 0; i < NPT; ++i)
-        for (int k = 0; k < 3; ++k) Q[i].v[k] = L.Q[i][k];
     pm::M3 R;
     pm::V3 t;
     double err2;
     rpp::abs_kernel<NPT>(c, Q, R, t, err2);
-    for (int k = 0; k < 3; ++k) { L.r1[k] = R.m[3 * k]; L.r2[k] = R.m[3 * k + 1]; L.r3[k] = R.m[3 * k + 2]; L.t[k] = t.v[k]; }
-    for (int i = 0; i < NPT; ++i)
-        for (int k = 0; k < 3; ++k) L.Q[i][k] = Q[i].v[k];
+    for (int k = 0; k < 3; ++k) { L.r1[k] = R.m[3 * k]; L.r2[k] = R.m[3 * k + 1]; }
+    refresh(ctx, stride, L);  // (t = tF sum F_i R P_i there as in the reference step)
     return err2;
 }
 
-// One AbsKernel step (RPP.cpp:229-332): consumes L.Q, produces R, t, the new L.Q and the error.
+// One AbsKernel step (RPP.cpp:229-332): from the current points (through L.a, L.b) to R, t, the new
+// points and their error.
 __device__ __forceinline__ double abs_kernel(const double* ctx, int stride, Lane& L)
 {
-    double a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
-    for (int i = 0; i < NPT; ++i) {
-        double fq[3];
-        apply_F(ctx, stride, i, L.Q[i], fq);
-        const double px = RPPF_C(C_PX + i), py = RPPF_C(C_PY + i);
-        for (int k = 0; k < 3; ++k) { a[k] += px * fq[k]; b[k] += py * fq[k]; }
-    }
-    const double S11 = a[0] * a[0] + a[1] * a[1] + a[2] * a[2], S22 = b[0] * b[0] + b[1] * b[1] + b[2] * b[2],
-                 S12 = a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
-    const double n0 = a[1] * b[2] - a[2] * b[1], n1 = a[2] * b[0] - a[0] * b[2], n2 = a[0] * b[1] - a[1] * b[0];
-    const double s = sqrt(n0 * n0 + n1 * n1 + n2 * n2), tr = S11 + S22;
-    if (!(s > 1e-10 * tr)) return abs_kernel_general(ctx, stride, L);
-    const double inv = 1.0 / (sqrt(tr + 2.0 * s) * s);
+    const double* a = L.a;
+    const double* b = L.b;
+    // products that only need (a, b): they issue beside the scalar chain below
+    double kxa[3], kxb[3], kya[3], kyb[3], kma[3], kmb[3], kta[3], ktb[3], gxa[3], gxb[3], gya[3], gyb[3];
+    symv(ctx, stride, C_KXX, a, kxa);
+    symv(ctx, stride, C_KXX, b, kxb);
+    symv(ctx, stride, C_KYY, a, kya);
+    symv(ctx, stride, C_KYY, b, kyb);
+    genv2(ctx, stride, C_KXY, a, a, kma, kta);   // Kxy a, Kxy^T a
+    genv2(ctx, stride, C_KXY, b, b, kmb, ktb);   // Kxy b, Kxy^T b
+    symv(ctx, stride, C_GX, a, gxa);
+    symv(ctx, stride, C_GX, b, gxb);
+    symv(ctx, stride, C_GY, a, gya);
+    symv(ctx, stride, C_GY, b, gyb);
+    const double S11 = fma(a[2], a[2], fma(a[1], a[1], a[0] * a[0])), S22 = fma(b[2], b[2], fma(b[1], b[1], b[0] * b[0])),
+                 S12 = fma(a[2], b[2], fma(a[1], b[1], a[0] * b[0]));
+    const double n0 = fma(a[1], b[2], -(a[2] * b[1])), n1 = fma(a[2], b[0], -(a[0] * b[2])), n2 = fma(a[0], b[1], -(a[1] * b[0]));
+    const double nn = fma(n2, n2, fma(n1, n1, n0 * n0)), tr = S11 + S22;
+    if (!(nn > 1e-20 * (tr * tr))) return abs_kernel_general(ctx, stride, L);  // s <= 1e-10 tr
+    // 1/s and 1/k from the reciprocal-square-root seed + two Newton steps (no sqrt, no division)
+    const double inv_s = fast_rsqrt(nn), s = nn * inv_s;
+    const double inv = fast_rsqrt(fma(2.0, s, tr)) * inv_s;
     const double c11 = (S22 + s) * inv, c12 = -S12 * inv, c22 = (S11 + s) * inv;
-    double r1[3], r2[3];
-    for (int k = 0; k < 3; ++k) { r1[k] = a[k] * c11 + b[k] * c12; r2[k] = a[k] * c12 + b[k] * c22; }
-    // t = tF * sum F_i (R P_i)
-    double sum[3] = {0, 0, 0}, t[3];
-    for (int i = 0; i < NPT; ++i) {
-        const double px = RPPF_C(C_PX + i), py = RPPF_C(C_PY + i);
-        double rp[3], f[3];
-        for (int k = 0; k < 3; ++k) rp[k] = r1[k] * px + r2[k] * py;
-        apply_F(ctx, stride, i, rp, f);
-        for (int k = 0; k < 3; ++k) sum[k] += f[k];
+    double r1[3], r2[3], gs[3], t[3], an[3], bn[3];
+    for (int k = 0; k < 3; ++k) {
+        an[k] = fma(c22, kmb[k], fma(c12, kxb[k] + kma[k], c11 * kxa[k]));
+        bn[k] = fma(c22, kyb[k], fma(c12, ktb[k] + kya[k], c11 * kta[k]));
+        r1[k] = fma(b[k], c12, a[k] * c11);
+        r2[k] = fma(b[k], c22, a[k] * c12);
+        gs[k] = fma(c22, gyb[k], fma(c12, gxb[k] + gya[k], c11 * gxa[k]));   // Gx r1 + Gy r2
     }
-    mul_tF(ctx, stride, sum, t);
+    symv(ctx, stride, C_TF, gs, t);   // t = tF * sum F_i (R P_i)
     if (t[2] < 0) return abs_kernel_general(ctx, stride, L);
-    for (int k = 0; k < 3; ++k) { L.r1[k] = r1[k]; L.r2[k] = r2[k]; L.t[k] = t[k]; }
-    L.r3[0] = r1[1] * r2[2] - r1[2] * r2[1];
-    L.r3[1] = r1[2] * r2[0] - r1[0] * r2[2];
-    L.r3[2] = r1[0] * r2[1] - r1[1] * r2[0];
-    return reproject(ctx, stride, L);
+    const double err2 = quad_error(ctx, stride, r1, r2, t, an, bn, gs);
+    for (int k = 0; k < 3; ++k) { L.r1[k] = r1[k]; L.r2[k] = r2[k]; L.t[k] = t[k]; L.a[k] = an[k]; L.b[k] = bn[k]; }
+    L.rays = false;
+    return err2;
 }
 
 // ObjPose with an initial rotation (RPP.cpp:98-128): t from R, Q_i, and the starting error.
+// (sum (F_i - I) R P_i = Gx r1 + Gy r2 because the model points are centred.)
 __device__ inline double init_from_R(const double* ctx, int stride, const double* R9, Lane& L)
 {
-    for (int k = 0; k < 3; ++k) { L.r1[k] = R9[3 * k]; L.r2[k] = R9[3 * k + 1]; L.r3[k] = R9[3 * k + 2]; }
-    double sum[3] = {0, 0, 0};
-    for (int i = 0; i < NPT; ++i) {
-        const double px = RPPF_C(C_PX + i), py = RPPF_C(C_PY + i);
-        double rp[3], f[3];
-        for (int k = 0; k < 3; ++k) rp[k] = L.r1[k] * px + L.r2[k] * py;
-        apply_F(ctx, stride, i, rp, f);
-        for (int k = 0; k < 3; ++k) sum[k] += f[k] - rp[k];
-    }
-    mul_tF(ctx, stride, sum, L.t);
-    return reproject(ctx, stride, L);
+    for (int k = 0; k < 3; ++k) { L.r1[k] = R9[3 * k]; L.r2[k] = R9[3 * k + 1]; }
+    return refresh(ctx, stride, L);
 }
 
 // End of ObjPose (RPP.cpp:176-207): R, t (un-centred), object- and image-space errors.
-__device__ inline void finalize(const double* ctx, int stride, const Lane& L, double new_err, double* R9, double* t3,
-                                double& obj_err, double& img_err)
+__device__ inline void finalize(const double* ctx, int stride, const Lane& L, double* R9, double* t3, double& obj_err, double& img_err)
 {
-    for (int k = 0; k < 3; ++k) { R9[3 * k] = L.r1[k]; R9[3 * k + 1] = L.r2[k]; R9[3 * k + 2] = L.r3[k]; }
-    obj_err = sqrt(new_err / NPT);
+    const double r3[3] = {L.r1[1] * L.r2[2] - L.r1[2] * L.r2[1], L.r1[2] * L.r2[0] - L.r1[0] * L.r2[2], L.r1[0] * L.r2[1] - L.r1[1] * L.r2[0]};
+    for (int k = 0; k < 3; ++k) { R9[3 * k] = L.r1[k]; R9[3 * k + 1] = L.r2[k]; R9[3 * k + 2] = r3[k]; }
+    obj_err = sqrt(point_error(ctx, stride, L) / NPT);
     double ie = 0;
     const double u0 = RPPF_C(C_VX + 0), v0 = RPPF_C(C_VY + 0);
     for (int i = 0; i < NPT; ++i) {
-        const double px = RPPF_C(C_PX + i), py = RPPF_C(C_PY + i);
         double q[3];
-        for (int k = 0; k < 3; ++k) q[k] = (L.r1[k] * px + L.r2[k] * py) + L.t[k];
+        point(ctx, stride, L, i, q);
         // reference quirk (RPP.cpp:197-198): every point is compared with image point 0
         const double xx = q[0] / q[2] - u0, yy = q[1] / q[2] - v0;
         ie += xx * xx + yy * yy;

@@ -29,6 +29,8 @@ def main():
     ctx.set_profiling(True)
     import ctypes
     clk = (ctypes.c_longlong * 16)()
+    ctx.localize_frames(frames, mantis_b200.MEM_DEVICE)  # untimed profiled pass (single-lane scratch)
+    ctx.stage_ms()
     ctx._lib.mantis_debug_clocks(ctx._h, None)
     ts = []
     for _ in range(iters):
@@ -41,6 +43,7 @@ def main():
     per = [round(v / (N * iters)) for v in clk]
     print('search kernel cycles/frame (first score, refinement, shifts, yaw windows):', per[:4])
     print('edge-link kernel cycles/frame (load, hysteresis, canny store, 3 morph passes, morph store, mask chain):', [per[4], per[5], per[8], per[9], per[6], per[7]])
+    print('ObjPose steps/frame spent in runs of <16, <64, <256, <1024, <4096, more steps:', per[10:16])
     print({k: round(v / iters, 2) for k, v in ms.items()})
     print(f"{W}x{H} x{N}: best {min(ts)*1e3:.1f} ms  -> {N/min(ts):.0f} frames/s")
 
