@@ -21,6 +21,7 @@ namespace cg = cooperative_groups;
 namespace {
 
 constexpr int LNT = 512;
+constexpr int PADR = 8;  // zero rows kept above local row 1 and below local row HC in every plane (largest k of the chain)
 
 // fill every run of M that contains a bit of S (S subset of M)
 __device__ __forceinline__ uint32_t flood_word(uint32_t M, uint32_t S)
@@ -219,6 +220,72 @@ __device__ __noinline__ void morph_op(cg::cluster_group& cluster, uint32_t* src,
     if (CS > 1) cluster.sync(); else __syncthreads();
 }
 
+// Same operation for a frame held by ONE CTA (the common case up to 640x480), with k and the row length known
+// at compile time.  A thread keeps one word column j and visits rows lr = 1 + tid / WW, + LNT / WW, ... so
+// that everything that depends on j (neighbour masks, the last word's mask) is loop-invariant, and the
+// column pass reads its 2k+1 rows at immediate offsets; rows outside the image are the zero rows every plane
+// carries (PADR of them), so neither pass tests a bound.  3k+7 and 3k+5 instructions per word instead of ~45 each.
+template <int K, int WWC>
+__device__ __forceinline__ void morph_fast_t(uint32_t* src, uint32_t* tmp, const Band& b, bool erode)
+{
+    const int WW = WWC ? WWC : b.WW;
+    const int R = LNT / WW;
+    const int tid = threadIdx.x;
+    const bool active = tid < R * WW;
+    const int rb = tid / WW, j = tid - rb * WW;
+    const uint32_t inv = erode ? 0xffffffffu : 0u;
+    const uint32_t mC = (j == WW - 1) ? b.last_mask : 0xffffffffu;
+    const uint32_t mL = j > 0 ? 0xffffffffu : 0u;
+    const uint32_t mR = (j + 1 < WW) ? ((j + 1 == WW - 1) ? b.last_mask : 0xffffffffu) : 0u;
+    if (active) {
+        for (int lr = 1 + rb; lr <= b.nrows; lr += R) {
+            const uint32_t* row = src + lr * WW + j;  // row[-1] / row[1] of the first / last word exist (halo rows) and are masked
+            const uint32_t C = (row[0] ^ inv) & mC, L = (row[-1] ^ inv) & mL, Rw = (row[1] ^ inv) & mR;
+            uint32_t acc = C;
+#pragma unroll
+            for (int d = 1; d <= K; ++d) acc |= __funnelshift_l(L, C, d) | __funnelshift_r(C, Rw, d);
+            tmp[lr * WW + j] = acc & mC;
+        }
+    }
+    __syncthreads();
+    if (active) {
+        for (int lr = 1 + rb; lr <= b.nrows; lr += R) {
+            const uint32_t* p = tmp + lr * WW + j;
+            uint32_t acc = p[0];
+#pragma unroll
+            for (int d = 1; d <= K; ++d) acc |= p[-d * WW] | p[d * WW];
+            src[lr * WW + j] = (acc ^ inv) & mC;
+        }
+    }
+    __syncthreads();
+}
+
+template <int WWC>
+__device__ __forceinline__ void morph_fast_k(uint32_t* src, uint32_t* tmp, const Band& b, int k, bool erode)
+{
+    switch (k) {
+    case 1: morph_fast_t<1, WWC>(src, tmp, b, erode); break;
+    case 2: morph_fast_t<2, WWC>(src, tmp, b, erode); break;
+    case 3: morph_fast_t<3, WWC>(src, tmp, b, erode); break;
+    case 4: morph_fast_t<4, WWC>(src, tmp, b, erode); break;
+    case 5: morph_fast_t<5, WWC>(src, tmp, b, erode); break;
+    default: morph_fast_t<8, WWC>(src, tmp, b, erode); break;
+    }
+}
+
+// k in {1, 2, 3, 4, 5, 8}: the iteration counts of the reference's chain (QuadDetection.h:213-214,
+// HypothesisEvaluation.h:352-371)
+__device__ __noinline__ void morph(cg::cluster_group& cluster, uint32_t* src, uint32_t* tmp, const Band& b, int k, bool erode,
+                                   int CS)
+{
+    if (CS == 1 && b.WW <= LNT / 2) {
+        if (b.WW == 20) morph_fast_k<20>(src, tmp, b, k, erode);
+        else morph_fast_k<0>(src, tmp, b, k, erode);
+    } else {
+        morph_op(cluster, src, tmp, b, k, erode, CS);
+    }
+}
+
 __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
 {
     extern __shared__ uint32_t smem[];
@@ -236,8 +303,14 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
     const int frame = blockIdx.x / CS;
     const int WW = b.WW, nrows = b.nrows;
 
-    uint32_t* A = smem;                      // weak, later ping-pong
-    uint32_t* B = smem + (b.HC + 2) * WW;    // edges
+    // every plane: PADR - 1 zero rows, halo row 0, rows 1..HC, halo row HC + 1, PADR - 1 zero rows
+    const int plane_words = (b.HC + 2 * PADR) * WW;
+    uint32_t* A = smem + (PADR - 1) * WW;                 // weak, later ping-pong
+    uint32_t* B = smem + plane_words + (PADR - 1) * WW;   // edges
+    for (int i = threadIdx.x; i < (PADR - 1) * WW; i += LNT) {
+        A[i - (PADR - 1) * WW] = 0u; B[i - (PADR - 1) * WW] = 0u;
+        A[(b.HC + 2) * WW + i] = 0u; B[(b.HC + 2) * WW + i] = 0u;
+    }
 
     const size_t plane = (size_t)frame * b.H * WW;
     for (int i = threadIdx.x; i < (b.HC + 2) * WW; i += LNT) {
@@ -307,8 +380,8 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
     if (want_morph) {
         // dilate x2, erode x1 on the closure result (B -> A -> B)
         if (CS > 1) cluster.sync(); else __syncthreads();
-        morph_op(cluster, B, A, b, 2, false, CS);
-        morph_op(cluster, B, A, b, 1, true, CS);
+        morph(cluster, B, A, b, 2, false, CS);
+        morph(cluster, B, A, b, 1, true, CS);
         tick(9);
         if (a.morph_u8) store_u8(B, b, a.morph_u8 + (size_t)frame * b.W * b.H);
         if (a.morph_bits) store_bits(B, b, a.morph_bits + plane);
@@ -342,12 +415,12 @@ __global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
         }
         // closes of 3, 4, 5 iterations then erode 3: dilate 3, erode 3, dilate 4, erode 4, dilate 5, erode 5 + 3
         if (CS > 1) cluster.sync(); else __syncthreads();
-        morph_op(cluster, B, A, b, 3, false, CS);
-        morph_op(cluster, B, A, b, 3, true, CS);
-        morph_op(cluster, B, A, b, 4, false, CS);
-        morph_op(cluster, B, A, b, 4, true, CS);
-        morph_op(cluster, B, A, b, 5, false, CS);
-        morph_op(cluster, B, A, b, 8, true, CS);
+        morph(cluster, B, A, b, 3, false, CS);
+        morph(cluster, B, A, b, 3, true, CS);
+        morph(cluster, B, A, b, 4, false, CS);
+        morph(cluster, B, A, b, 4, true, CS);
+        morph(cluster, B, A, b, 5, false, CS);
+        morph(cluster, B, A, b, 8, true, CS);
         if (a.mask_u8) store_u8(B, b, a.mask_u8 + (size_t)frame * b.W * b.H);
         if (a.mask_bits) store_bits(B, b, a.mask_bits + plane);
     }
@@ -370,7 +443,7 @@ int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_st
     for (int pass = 0; pass < 2 && chosen < 0; ++pass)
         for (cs = 1; cs <= 8; cs *= 2) {
             int hc = (h + cs - 1) / cs;
-            smem = (size_t)2 * (hc + 2) * WW * sizeof(uint32_t);
+            smem = (size_t)2 * (hc + 2 * PADR) * WW * sizeof(uint32_t);
             if (smem <= (pass == 0 ? want : hard)) { chosen = cs; break; }
         }
     if (chosen < 0) {
@@ -385,7 +458,7 @@ int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_st
     a.W = w; a.H = h; a.WW = WW; a.HC = (h + cs - 1) / cs;
     if ((a.mask_bits || a.mask_u8) && !a.canny_bits) return MANTIS_ERR_INVALID;
     a.dbg = (long long*)c->dbg_clocks;
-    smem = (size_t)2 * (a.HC + 2) * WW * sizeof(uint32_t);
+    smem = (size_t)2 * (a.HC + 2 * PADR) * WW * sizeof(uint32_t);
 
     MCHECK(c, cudaFuncSetAttribute(k_edge_link, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
