@@ -100,3 +100,56 @@ def test_localize_full_hd_with_noise_and_blur(ctx):
         assert np.array_equal(canny[i], oc) and np.array_equal(morph[i], om)
         otr, _ = po.localize(frames[i], K, D)
         assert compare(res[i], tr[i], otr, strict=False) or res[i].status != 0
+
+
+def _rz(k):
+    c, s = np.cos(k * np.pi / 2), np.sin(k * np.pi / 2)
+    return np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]])
+
+
+def _qmat(q):
+    x, y, z, w = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+def test_localize_full_batch_properties(ctx):
+    """BASELINE.json configs[1] at full size (4096 frames 640x480, rendered on the device, device-resident):
+    size-independent properties -- determinism, batch invariance, oracle parity on a sample, and the
+    render -> localize round trip modulo the grid's symmetry group (quarter turns about z; the reference's
+    own accuracy, not ours, sets the tolerance: sigma 0.03 rad perturbations, PoseAdjustment.h:29)."""
+    import torch
+
+    import mantis_b200
+
+    W, H, N = 640, 480, 4096
+    K, D = K_for(W, H), np.zeros(4)
+    ps = poses(N, seed=0x4D414E54 + 2)
+    buf = torch.empty((N, H, W, 3), dtype=torch.uint8, device="cuda:0")
+    ctx.render_grid_device(ps, W, H, K, D, buf.data_ptr())
+    torch.cuda.synchronize()
+    ptrs = [buf.data_ptr() + i * H * W * 3 for i in range(N)]
+    res, _ = ctx.localize_frames(ctx.make_frames(ptrs, W, H, K, D), mantis_b200.MEM_DEVICE)
+    assert all(r.status == 0 for r in res)
+    # determinism: the same call again gives the same bytes
+    res2, _ = ctx.localize_frames(ctx.make_frames(ptrs, W, H, K, D), mantis_b200.MEM_DEVICE)
+    assert bytes(res) == bytes(res2)
+    # batch invariance: a slice localized on its own (other chunking, other lanes) gives the same records
+    sub, tr_sub = ctx.localize_frames(ctx.make_frames(ptrs[1000:1064], W, H, K, D), mantis_b200.MEM_DEVICE, want_trace=True)
+    assert bytes(sub) == bytes(res)[1000 * len(bytes(sub)) // 64:1064 * len(bytes(sub)) // 64]
+    # oracle parity on a sample of the slice
+    same = 0
+    for i in (0, 13, 27, 41, 55, 63):
+        frame = buf[1000 + i].cpu().numpy()
+        otr, _ = po.localize(frame, K, D)
+        same += compare(sub[i], tr_sub[i], otr, strict=False)
+    assert same >= 5
+    # round trip modulo the symmetry group
+    ang, dz = [], []
+    for i in range(N):
+        Rg = _qmat(res[i].quat_xyzw[:])
+        ang.append(min(np.arccos(np.clip((np.trace(Rg.T @ (_rz(k) @ ps[i][0])) - 1) / 2, -1, 1)) for k in range(4)))
+        dz.append(abs(res[i].pos[2] - ps[i][1][2]))
+    assert max(ang) < 0.25 and np.median(ang) < 0.06
+    assert max(dz) < 0.3 and np.median(dz) < 0.06
