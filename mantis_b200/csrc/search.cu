@@ -97,14 +97,15 @@ __device__ __forceinline__ PoseXY load_pose(const Tf& c2w)
     p.full = &c2w;
     return p;
 }
-__device__ __forceinline__ bool project(const PoseXY& P, const CamK& cam, double px, double py, double pz, bool planar,
-                                        const double2* __restrict__ atan_tab, int W, int H, double& u, double& v)
+template <bool PLANAR>
+__device__ __forceinline__ bool project(const PoseXY& P, const CamK& cam, double px, double py, double pz,
+                                        const double2* __restrict__ atan_tab, double W, double H, double& u, double& v)
 {
     double c[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         double acc = fma(P.rx[i], px, fma(P.ry[i], py, P.t[i]));
-        if (!planar) acc = fma(P.full->R[i * 3 + 2], pz, acc);  // the map is the floor plane: z = 0 adds nothing
+        if (!PLANAR) acc = fma(P.full->R[i * 3 + 2], pz, acc);  // the map is the floor plane: z = 0 adds nothing
         c[i] = acc;
     }
     if (!(c[2] > 1e-300)) return false;  // behind the camera (the reference's z > 0), or no usable reciprocal
@@ -142,6 +143,7 @@ struct SearchArgs {
     const Tf* rand_tf;  // [iterations * particles]
     const double* shifts;  // [n_shift][2]
     int n_shift, iterations, particles;
+    double Wd, Hd;  // frame size as doubles (the in-frame test compares doubles)
     Tf rotz;
     double projection_bias, color_bias;
     mantis_result* out;
@@ -168,8 +170,8 @@ struct Shared {
 // score `nh` hypotheses (c2w via the accessor) against all map points on the masked image.
 // The (hypothesis, 32-point chunk) tasks are cut into one contiguous range per warp, so a warp
 // reduces and publishes once per hypothesis it touches instead of once per chunk.
-template <class GetC2W>
-__device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map, bool planar, int nh, double bias,
+template <bool PLANAR, class GetC2W>
+__device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map, double Wd, double Hd, int nh, double bias,
                             GetC2W get)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -211,7 +213,7 @@ __device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map
         const int pi = ch * 32 + lane;
         if (pi < n_map) {
             double u, v;
-            if (project(c2w, cam, s.map_x[pi], s.map_y[pi], planar ? 0.0 : s.map_z[pi], planar, s.atan_tab, im.W, im.H, u, v)) {
+            if (project<PLANAR>(c2w, cam, s.map_x[pi], s.map_y[pi], PLANAR ? 0.0 : s.map_z[pi], s.atan_tab, Wd, Hd, u, v)) {
                 ++ok_acc;
                 const int x = __double2int_rn(u), y = __double2int_rn(v);
                 const unsigned off = (unsigned)(y * im.stride + 3 * x);
@@ -240,6 +242,7 @@ __device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map
     __syncthreads();
 }
 
+template <bool PLANAR>
 __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -282,7 +285,6 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
         cam.D0 = c0.D[0]; cam.D1 = c0.D[1]; cam.D2 = c0.D[2]; cam.D3 = c0.D[3];
         cam.has_dist = c0.D[0] != 0 || c0.D[1] != 0 || c0.D[2] != 0 || c0.D[3] != 0;
     }
-    const bool planar = a.map_planar != 0;
     const Hyp* hyps = a.hyps + (size_t)frame * MANTIS_MAX_HYPS;
     const short* sel = a.sel + (size_t)frame * MANTIS_MAX_HYPS;
     for (int i = tid; i < a.n_map; i += SNT) {
@@ -296,7 +298,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     };
 
     // (6) evaluateHypotheses on the kept cluster, (7) best 1
-    score_white(s, im, cam, a.n_map, planar, n_sel, a.projection_bias, [&](int h) -> const Tf& { return hyps[sel[h]].c2w; });
+    score_white<PLANAR>(s, im, cam, a.n_map, a.Wd, a.Hd, n_sel, a.projection_bias, [&](int h) -> const Tf& { return hyps[sel[h]].c2w; });
     if (tid == 0) {
         int bi = 0;  // stable descending sort, last element: minimal error, highest index among ties
         for (int i = 1; i < n_sel; ++i)
@@ -315,7 +317,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
             pm::tf_inv(s.cand_w2c[tid], s.cand_c2w[tid]);
         }
         __syncthreads();
-        score_white(s, im, cam, a.n_map, planar, a.particles, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
+        score_white<PLANAR>(s, im, cam, a.n_map, a.Wd, a.Hd, a.particles, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
         if (tid == 0) {
             int bp = -1;
             double be = s.best.error;
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
         pm::tf_inv(w, s.cand_c2w[tid]);
     }
     __syncthreads();
-    score_white(s, im, cam, a.n_map, planar, ns, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
+    score_white<PLANAR>(s, im, cam, a.n_map, a.Wd, a.Hd, ns, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
     if (tr)
         for (int i = tid; i < ns && i < 81; i += SNT) tr->shift_err[i] = s.err[i];
     // (11) best 20: position in a stable descending sort; keep the last 20
@@ -379,7 +381,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     for (int item = tid; item < nrot * ng; item += SNT) {
         const int h = item / ng, gi = item - h * ng, mi = a.n_green_off + gi;
         double u, v;
-        const bool ok = project(load_pose(s_rot_c2w[h]), cam, s.map_x[mi], s.map_y[mi], s.map_z[mi], planar, s.atan_tab, im.W, im.H, u, v);
+        const bool ok = project<PLANAR>(load_pose(s_rot_c2w[h]), cam, s.map_x[mi], s.map_y[mi], s.map_z[mi], s.atan_tab, a.Wd, a.Hd, u, v);
         const int slot = h * 40 + gi;
         s.green_acc[slot] = 0;
         s.green_xy[slot] = ok ? ((__double2int_rn(u) & 0xffff) | (__double2int_rn(v) << 16)) : -1;
@@ -471,6 +473,7 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
     a.bgr = d_bgr; a.pitch = pitch; a.stride = stride;
     a.mask_bits = d_mask_bits;
     a.W = w; a.H = h; a.WW = words_per_row(w);
+    a.Wd = (double)w; a.Hd = (double)h;
     a.cams = d_cams; a.quads = d_quads; a.hyps = d_hyps; a.sel = d_sel; a.info = d_info;
     a.map = (const double*)c->d_map.p;
     a.n_map = c->n_map; a.n_green_off = c->n_map - c->n_green; a.n_green = c->n_green;
@@ -485,8 +488,13 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
     a.out = d_out; a.trace = d_trace;
     a.dbg = (long long*)c->dbg_clocks;
     const size_t smem = sizeof(Shared);
-    MCHECK(c, cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_search<<<n, SNT, smem, c->stream>>>(a);
+    if (c->map_planar) {
+        MCHECK(c, cudaFuncSetAttribute(k_search<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_search<true><<<n, SNT, smem, c->stream>>>(a);
+    } else {
+        MCHECK(c, cudaFuncSetAttribute(k_search<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_search<false><<<n, SNT, smem, c->stream>>>(a);
+    }
     c->launches++;
     MCHECK(c, cudaGetLastError());
     return MANTIS_OK;
