@@ -191,18 +191,23 @@ __device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map
     //   stage 3 (task t-2)  add the colour error
     uint32_t m_word = 0;
     int m_key = -1;  // (pixel byte offset << 5) | mask bit, -1 = nothing pending
-    int pb = 255, pg = 255, pr = 255;  // pixel bytes in flight; white = no contribution
+    // pixel in flight: the two aligned words that hold its three bytes, and the byte shift.  All ones = white =
+    // no contribution; err = sum (255 - c)^2 is one IDP.4A on the complemented pixel.
+    uint32_t w0 = ~0u, w1 = ~0u, sh8 = 0u;
     auto stage3 = [&]() {
-        const int db = pb - 255, dg = pg - 255, dr = pr - 255;
-        e_acc += db * db + dg * dg + dr * dr;
-        pb = pg = pr = 255;
+        const uint32_t inv = ~__funnelshift_r(w0, w1, sh8) & 0xffffffu;
+        e_acc = (int)__dp4a(inv, inv, (uint32_t)e_acc);
+        w0 = w1 = ~0u;
     };
     auto stage2 = [&]() {
         if (m_key >= 0) {
-            pb = pg = pr = 0;
+            w0 = w1 = 0u;  // masked out = black
             if ((m_word >> (m_key & 31)) & 1u) {
-                const uint8_t* p = im.bgr + ((unsigned)m_key >> 5);
-                pb = __ldg(p); pg = __ldg(p + 1); pr = __ldg(p + 2);
+                const uintptr_t p = (uintptr_t)im.bgr + ((unsigned)m_key >> 5);
+                const uint32_t* q = reinterpret_cast<const uint32_t*>(p & ~(uintptr_t)3);
+                sh8 = ((unsigned)p & 3u) << 3;
+                w0 = __ldg(q);
+                if (sh8 >= 16u) w1 = __ldg(q + 1);  // the third byte sits in the next word
             }
             m_key = -1;
         }
