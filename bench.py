@@ -230,9 +230,10 @@ def main():
     ms = max_over_ranks(e0.elapsed_time(e1))
     value = world * B * args.steps / (ms * 1e-3)
 
-    # ---- per-stage device times: the same K steps once more with the library's stage events on.  Stage
-    # events need the stages back to back on one stream, so this pass runs single-lane (the timed pass above
-    # overlaps several lanes, which is where `value` comes from); the image-stage kernels are timed here.
+    # ---- per-stage device times: the same K steps once more with the library's stage events on (CUDA events
+    # on the library's stream between the stages).  The library runs one lane by default, so this pass and
+    # the timed pass above execute the same launches; with MANTIS_LANES >= 2 the timed pass would overlap
+    # lanes and this one would not.  The image-stage kernels are timed here.
     ctx.set_profiling(True)
     ctx.localize_frames(dframes, mantis_b200.MEM_DEVICE)  # untimed: the single-lane path sizes its own scratch here
     ctx.stage_ms()
@@ -256,13 +257,16 @@ def main():
                 "peak_source": peak_src, "algorithmic_bytes_per_frame": 4 * W * H,
                 "image_stage_frames_per_s": B / (img_ms * 1e-3),
                 "share_of_step": img_ms / (ms_single / args.steps),
-                "timing": "CUDA events around K1 and K2 on the library stream, in a second pass of the same K steps run "
-                          "single-lane (stage events need the kernels back to back); the headline pass overlaps lanes"}
+                "timing": "CUDA events around K1 and K2 on the library stream, in a second pass of the same K steps "
+                          "(same launches as the headline pass, plus the stage events)"}
     prof = os.path.join(ROOT, "profiles", "image_stage_traffic.json")
     if os.path.exists(prof):
         try:
             with open(prof) as f:
-                roofline["traffic"] = json.load(f).get("dram_bytes_per_frame")
+                per_frame = json.load(f).get("dram_bytes_per_frame")
+                roofline["traffic_bytes_per_frame"] = per_frame  # ncu dram read + write of K1 + K2, per frame
+                roofline["traffic"] = per_frame * B if per_frame else None  # per launch pair, like `achieved`'s numerator
+                roofline["algorithmic_bytes_per_launch"] = alg_bytes
         except (OSError, ValueError):
             pass
 
@@ -299,7 +303,7 @@ def main():
                "config": workload(B, world), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
                "roofline": roofline,
                "stage_ms_per_step": {k: v / args.steps for k, v in stage.items()},
-               "single_lane_ms_per_step": ms_single / args.steps, "lanes": int(os.environ.get("MANTIS_LANES", "3")),
+               "single_lane_ms_per_step": ms_single / args.steps, "lanes": int(os.environ.get("MANTIS_LANES", "1")),
                "frame_status_histogram": dict(zip(["ok", "no_quads", "no_hypotheses", "yaw_failed", "overflow"], status))}
         if cpu is not None:
             out["cpu_baseline"] = cpu

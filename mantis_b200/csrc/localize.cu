@@ -127,11 +127,12 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     }
     MCHECK(c, cudaSetDevice(c->device));
 
-    // Large device-resident batches are split over a few lanes (child contexts: own stream, own scratch;
-    // MANTIS_LANES, default 3) driven by one host thread each, so that the latency-bound kernels of one part (border walks,
-    // RPP iterations) share the SMs with whatever the other parts are running.  Per-stage profiling needs the
-    // stages back to back on one stream, so it keeps the single-lane path.
-    static const int lanes_env = []() { const char* e = getenv("MANTIS_LANES"); return e ? atoi(e) : 3; }();
+    // Large device-resident batches CAN be split over a few lanes (child contexts: own stream, own scratch;
+    // MANTIS_LANES >= 2) driven by one host thread each, so that the latency-bound kernels of one part (border
+    // walks, RPP iterations) share the SMs with whatever the other parts are running.  That paid while those
+    // kernels were slow; with the current ones a single lane is the fastest (29.3 / 30.1 / 30.5 ms per 4096
+    // frames for 1 / 2 / 3 lanes), so the default is 1.  Per-stage profiling always uses the single-lane path.
+    static const int lanes_env = []() { const char* e = getenv("MANTIS_LANES"); return e ? atoi(e) : 1; }();
     const int L = lanes_env > mantis_ctx::MAX_LANES ? mantis_ctx::MAX_LANES : lanes_env;
     if (mem == MANTIS_MEM_DEVICE && !c->is_lane && !c->profiling && L >= 2 && n >= 512 * L) {
         for (int i = 0; i < L; ++i)
