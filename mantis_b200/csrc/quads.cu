@@ -412,6 +412,9 @@ struct QuadArgs {
     short* hole_owner;    // [n][MAXB] that border, for the hole borders
     uint32_t* cut_dst;    // [n][MAXCUT] (offset of the piece's vertices in its frame << 10) | border
     int use_cuts;
+    int cut_mask;             // cut rows are y & cut_mask == 0 (CUT_ROWS - 1 up to VGA, wider spacing for larger frames)
+    const uint32_t* padded;   // zero-framed copies of the planes in global memory (PadImg layout) when a plane does not fit in shared memory
+    size_t pad_words;         // words per padded plane
     FrameQuads* out;
     double eps, stretch, radius_mult;
 };
@@ -519,6 +522,28 @@ __device__ __forceinline__ PadImg stage_padded(const uint32_t* g, int H, int WW)
     return im;
 }
 
+// The same layout in global memory, for frames whose plane does not fit in shared memory (1920x1080): the
+// walkers then read it through L1 / L2 (268 KB per frame).
+__device__ __forceinline__ PadImg global_padded(const QuadArgs& a, int frame)
+{
+    PadImg im;
+    im.base = a.padded + (size_t)frame * a.pad_words;
+    im.stride = a.WW + 2;
+    return im;
+}
+
+__global__ void __launch_bounds__(CNT) k_qpad(QuadArgs a, uint32_t* dst)
+{
+    const int frame = blockIdx.y, H = a.H, WW = a.WW;
+    const uint32_t* g = a.morph_bits + (size_t)frame * H * WW;
+    uint32_t* d = dst + (size_t)frame * a.pad_words;
+    const int stride = WW + 2, total = (H + 2) * stride;
+    for (int i = blockIdx.x * CNT + threadIdx.x; i < total; i += gridDim.x * CNT) {
+        const int r = i / stride, cidx = i - r * stride;
+        d[i] = (r >= 1 && r <= H && cidx >= 1 && cidx <= WW) ? __ldg(g + (size_t)(r - 1) * WW + (cidx - 1)) : 0u;
+    }
+}
+
 template <class Img>
 __device__ __forceinline__ void probe_frame(const QuadArgs& a, const Img& im, int frame)
 {
@@ -555,8 +580,10 @@ __global__ void __launch_bounds__(CNT) k_qprobe(QuadArgs a, int use_smem)
     const int frame = blockIdx.x;
     if (a.use_cuts && !a.meta[frame].fallback) return;
     const uint32_t* g = a.morph_bits + (size_t)frame * a.H * a.WW;
-    if (use_smem) {
+    if (use_smem == 1) {
         probe_frame(a, stage_padded(g, a.H, a.WW), frame);
+    } else if (use_smem == 2) {
+        probe_frame(a, global_padded(a, frame), frame);
     } else {
         BitImg im;
         im.bits = g; im.W = a.W; im.H = a.H; im.WW = a.WW;
@@ -649,9 +676,12 @@ __global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a, int use_smem)
     const int frame = blockIdx.x;
     if (a.use_cuts && !a.meta[frame].fallback) return;
     const uint32_t* g = a.morph_bits + (size_t)frame * a.H * a.WW;
-    if (use_smem) {
+    if (use_smem == 1) {
         if (a.meta[frame].flags || a.meta[frame].nb == 0) return;
         trace_frame(a, stage_padded(g, a.H, a.WW), frame);
+    } else if (use_smem == 2) {
+        if (a.meta[frame].flags || a.meta[frame].nb == 0) return;
+        trace_frame(a, global_padded(a, frame), frame);
     } else {
         BitImg im;
         im.bits = g; im.W = a.W; im.H = a.H; im.WW = a.WW;
@@ -687,7 +717,7 @@ constexpr uint32_t EMPTY = 0xffffffffu;
 // candidate visits of the frame, keyed (pixel << 1) | (1 if it is the East side)
 struct CutSet {
     uint32_t* tab;  // [TABN], shared
-    int W;
+    int W, mask;
     static __device__ __forceinline__ uint32_t slot(uint32_t k) { return (k * 2654435761u) >> 21; }  // TABN = 2^11
     __device__ __forceinline__ void insert(uint32_t k)
     {
@@ -706,8 +736,8 @@ struct CutSet {
     }
     __device__ __forceinline__ bool cand_west(int x, int y, uint32_t nb) const { return (nb & 0x0eu) == 0u && has((uint32_t)(y * W + x) << 1); }
     __device__ __forceinline__ bool cand_east(int x, int y, uint32_t nb) const { return (nb & 0x02u) != 0u && has(((uint32_t)(y * W + x) << 1) | 1u); }
-    __device__ __forceinline__ bool cut_west(int x, int y, uint32_t nb) const { return (y & (CUT_ROWS - 1)) == 0 || cand_west(x, y, nb); }
-    __device__ __forceinline__ bool cut_east(int x, int y, uint32_t nb) const { return (y & (CUT_ROWS - 1)) == 0 || cand_east(x, y, nb); }
+    __device__ __forceinline__ bool cut_west(int x, int y, uint32_t nb) const { return (y & mask) == 0 || cand_west(x, y, nb); }
+    __device__ __forceinline__ bool cut_east(int x, int y, uint32_t nb) const { return (y & mask) == 0 || cand_east(x, y, nb); }
     // is the visit at (x, y) that examined the background directions z a cut?
     __device__ __forceinline__ bool is_cut(int x, int y, uint32_t nb, uint32_t z) const
     {
@@ -730,7 +760,7 @@ __global__ void __launch_bounds__(CNT) k_qcut(QuadArgs a)
             if (atomicAdd(&meta->ncc, 1) >= MAXCC || k >= MAXCUT) { meta->fallback = 1; return; }
             dst[k] = is_hole ? ((((uint32_t)(y * W + x - 1)) << 2) | 3u) : ((((uint32_t)(y * W + x)) << 2) | 1u);
         });
-        if (!c || (y & (CUT_ROWS - 1))) continue;
+        if (!c || (y & a.cut_mask)) continue;
         const uint32_t cp = bits_at(bits, WW, H, y, j - 1), cn = bits_at(bits, WW, H, y, j + 1);
         uint32_t west = c & ~((c << 1) | (cp >> 31));   // foreground with background to the West
         uint32_t east = c & ~((c >> 1) | (cn << 31));   // ... to the East
@@ -791,6 +821,7 @@ __device__ __forceinline__ int back_dir(uint32_t nb, int side)
     return (side + 31 - __clz((int)rot)) & 7;
 }
 
+template <bool GPAD>
 __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
 {
     __shared__ uint32_t s_tab[TABN];
@@ -799,14 +830,16 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
     if (meta->fallback) return;
     const int ncut = meta->ncut;
     const size_t base = (size_t)frame * MAXCUT;
-    CutSet cs{s_tab, W};
+    CutSet cs{s_tab, W, a.cut_mask};
     for (int i = threadIdx.x; i < TABN; i += CNT) s_tab[i] = EMPTY;
     __syncthreads();
     for (int i = threadIdx.x; i < ncut; i += CNT) {
         const uint32_t raw = a.cut[base + i];
         if (raw & 1u) cs.insert(raw >> 1);
     }
-    const PadImg im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
+    PadImg im;
+    if (GPAD) { im = global_padded(a, frame); __syncthreads(); }
+    else im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
     for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
         const uint32_t raw = a.cut[base + slot];
         const bool east = raw & 2u;
@@ -961,6 +994,7 @@ __global__ void __launch_bounds__(LNT) k_qlink(QuadArgs a)
         if (s_key[s_start[n]] & KEY_RCAND) a.hole_owner[bbase + s_rank[n]] = (short)(a.cut_dst[base + s_par[n]] & 1023u);
 }
 
+template <bool GPAD>
 __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
 {
     __shared__ uint32_t s_tab[TABN];
@@ -969,7 +1003,7 @@ __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
     if (meta->fallback || meta->flags || meta->nb == 0) return;
     const int ncut = meta->ncut;
     const size_t base = (size_t)frame * MAXCUT;
-    CutSet cs{s_tab, W};
+    CutSet cs{s_tab, W, a.cut_mask};
     for (int i = threadIdx.x; i < TABN; i += CNT) s_tab[i] = EMPTY;
     __syncthreads();
     for (int i = threadIdx.x; i < ncut; i += CNT) {
@@ -978,7 +1012,9 @@ __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
         if (key & KEY_LTOP) cs.insert(((key & KEY_STATE) >> 3) << 1);
         if (key & KEY_RCAND) cs.insert((((key & KEY_STATE) >> 3) << 1) | 1u);
     }
-    const PadImg im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
+    PadImg im;
+    if (GPAD) { im = global_padded(a, frame); __syncthreads(); }
+    else im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
     for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
         const uint32_t d = a.cut_dst[base + slot];
         if (d == EMPTY) continue;
@@ -1230,27 +1266,38 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     a.radius_mult = c->cfg.search_radius_multiplier;
     MCHECK(c, cudaMemsetAsync(a.meta, 0, (size_t)n * sizeof(QMeta), c->stream));
     const size_t plane = (size_t)(h + 2) * (a.WW + 2) * sizeof(uint32_t);
-    const int use_smem = plane <= 200 * 1024;
-    a.use_cuts = use_smem && (size_t)w * h < (1u << 21) && !getenv("MANTIS_QUADS_SEQUENTIAL");  // (the variable is for tests)
-    if (use_smem) {
+    // 1 = the plane is staged in shared memory; 2 = it does not fit (1920x1080): zero-framed copy in global memory
+    const int use_smem = plane <= 200 * 1024 ? 1 : 2;
+    // piece keys hold (pixel << 3 | direction) in 24 bits
+    a.use_cuts = (size_t)w * h < (1u << 21) && !getenv("MANTIS_QUADS_SEQUENTIAL");  // (the variable is for tests)
+    a.cut_mask = (h <= 512 ? CUT_ROWS : h <= 1024 ? 2 * CUT_ROWS : 4 * CUT_ROWS) - 1;  // about the same number of cut rows per frame
+    a.padded = nullptr; a.pad_words = plane / sizeof(uint32_t);
+    if (use_smem == 1) {
         MCHECK(c, cudaFuncSetAttribute(k_qprobe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
         MCHECK(c, cudaFuncSetAttribute(k_qtrace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
-        MCHECK(c, cudaFuncSetAttribute(k_qseg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
-        MCHECK(c, cudaFuncSetAttribute(k_qemit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
+        MCHECK(c, cudaFuncSetAttribute(k_qseg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
+        MCHECK(c, cudaFuncSetAttribute(k_qemit<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plane));
+    } else {
+        if ((rc = ctx_reserve(c, c->q_pad, (size_t)n * plane))) return rc;
+        a.padded = (const uint32_t*)c->q_pad.p;
+        k_qpad<<<dim3(8, n), CNT, 0, c->stream>>>(a, (uint32_t*)c->q_pad.p);
+        c->launches += 1;
     }
     if (a.use_cuts) {
         k_qcut<<<dim3(4, n), CNT, 0, c->stream>>>(a);
-        k_qseg<<<n, CNT, plane, c->stream>>>(a);
+        if (use_smem == 1) k_qseg<false><<<n, CNT, plane, c->stream>>>(a);
+        else k_qseg<true><<<n, CNT, 0, c->stream>>>(a);
         k_qlink<<<n, LNT, 0, c->stream>>>(a);
         c->launches += 3;
     }
     // the sequential route: all frames when the plane does not fit in shared memory, else only the frames flagged above
     k_qcand<<<dim3(a.use_cuts ? 2 : 16, n), CNT, 0, c->stream>>>(a);
-    k_qprobe<<<n, CNT, use_smem ? plane : 0, c->stream>>>(a, use_smem);
+    k_qprobe<<<n, CNT, use_smem == 1 ? plane : 0, c->stream>>>(a, use_smem);
     k_qrank<<<n, CNT, 0, c->stream>>>(a);
-    k_qtrace<<<n, TNT, use_smem ? plane : 0, c->stream>>>(a, use_smem);
+    k_qtrace<<<n, TNT, use_smem == 1 ? plane : 0, c->stream>>>(a, use_smem);
     if (a.use_cuts) {
-        k_qemit<<<n, CNT, plane, c->stream>>>(a);
+        if (use_smem == 1) k_qemit<false><<<n, CNT, plane, c->stream>>>(a);
+        else k_qemit<true><<<n, CNT, 0, c->stream>>>(a);
         c->launches += 1;
     }
     k_qapprox_long<<<n, 32 * LWARPS, 0, c->stream>>>(a);
