@@ -226,7 +226,8 @@ __device__ __noinline__ void morph_op(cg::cluster_group& cluster, uint32_t* src,
 // column pass reads its 2k+1 rows at immediate offsets; rows outside the image are the zero rows every plane
 // carries (PADR of them), so neither pass tests a bound.  3k+7 and 3k+5 instructions per word instead of ~45 each.
 template <int K, int WWC>
-__device__ __forceinline__ void morph_fast_t(uint32_t* src, uint32_t* tmp, const Band& b, bool erode)
+__device__ __forceinline__ void morph_fast_t(cg::cluster_group& cluster, uint32_t* src, uint32_t* tmp, const Band& b, bool erode,
+                                             int CS)
 {
     const int WW = WWC ? WWC : b.WW;
     const int R = LNT / WW;
@@ -247,7 +248,22 @@ __device__ __forceinline__ void morph_fast_t(uint32_t* src, uint32_t* tmp, const
             tmp[lr * WW + j] = acc & mC;
         }
     }
-    __syncthreads();
+    if (CS > 1) {
+        // a frame split over a cluster: the K rows on either side of the band come from the neighbours' planes
+        // (DSMEM) into this plane's pad rows, so that the column pass below stays local and branch-free
+        cluster.sync();  // every CTA has written its rows of tmp
+        const uint32_t* up = (b.rank > 0 && b.nrows > 0) ? cluster.map_shared_rank(tmp, b.rank - 1) : nullptr;
+        const uint32_t* dn = b.rank < b.last_rank ? cluster.map_shared_rank(tmp, b.rank + 1) : nullptr;
+        const int down_rows = dn ? min(b.HC, b.H - (b.rank + 1) * b.HC) : 0;
+        for (int i = tid; i < K * WW; i += LNT) {
+            const int r = i / WW, jj = i - r * WW;
+            if (up) tmp[-r * WW + jj] = up[(b.HC - r) * WW + jj];  // every non-last CTA owns exactly HC rows
+            if (dn) tmp[(b.nrows + 1 + r) * WW + jj] = r < down_rows ? dn[(1 + r) * WW + jj] : 0u;
+        }
+        cluster.sync();  // all pulls done before anyone overwrites tmp again
+    } else {
+        __syncthreads();
+    }
     if (active) {
         for (int lr = 1 + rb; lr <= b.nrows; lr += R) {
             const uint32_t* p = tmp + lr * WW + j;
@@ -261,15 +277,16 @@ __device__ __forceinline__ void morph_fast_t(uint32_t* src, uint32_t* tmp, const
 }
 
 template <int WWC>
-__device__ __forceinline__ void morph_fast_k(uint32_t* src, uint32_t* tmp, const Band& b, int k, bool erode)
+__device__ __forceinline__ void morph_fast_k(cg::cluster_group& cluster, uint32_t* src, uint32_t* tmp, const Band& b, int k,
+                                             bool erode, int CS)
 {
     switch (k) {
-    case 1: morph_fast_t<1, WWC>(src, tmp, b, erode); break;
-    case 2: morph_fast_t<2, WWC>(src, tmp, b, erode); break;
-    case 3: morph_fast_t<3, WWC>(src, tmp, b, erode); break;
-    case 4: morph_fast_t<4, WWC>(src, tmp, b, erode); break;
-    case 5: morph_fast_t<5, WWC>(src, tmp, b, erode); break;
-    default: morph_fast_t<8, WWC>(src, tmp, b, erode); break;
+    case 1: morph_fast_t<1, WWC>(cluster, src, tmp, b, erode, CS); break;
+    case 2: morph_fast_t<2, WWC>(cluster, src, tmp, b, erode, CS); break;
+    case 3: morph_fast_t<3, WWC>(cluster, src, tmp, b, erode, CS); break;
+    case 4: morph_fast_t<4, WWC>(cluster, src, tmp, b, erode, CS); break;
+    case 5: morph_fast_t<5, WWC>(cluster, src, tmp, b, erode, CS); break;
+    default: morph_fast_t<8, WWC>(cluster, src, tmp, b, erode, CS); break;
     }
 }
 
@@ -278,15 +295,15 @@ __device__ __forceinline__ void morph_fast_k(uint32_t* src, uint32_t* tmp, const
 __device__ __noinline__ void morph(cg::cluster_group& cluster, uint32_t* src, uint32_t* tmp, const Band& b, int k, bool erode,
                                    int CS)
 {
-    if (CS == 1 && b.WW <= LNT / 2) {
-        if (b.WW == 20) morph_fast_k<20>(src, tmp, b, k, erode);
-        else morph_fast_k<0>(src, tmp, b, k, erode);
+    if (b.WW <= LNT / 2 && (CS == 1 || b.HC >= PADR)) {
+        if (b.WW == 20) morph_fast_k<20>(cluster, src, tmp, b, k, erode, CS);
+        else morph_fast_k<0>(cluster, src, tmp, b, k, erode, CS);
     } else {
         morph_op(cluster, src, tmp, b, k, erode, CS);
     }
 }
 
-__global__ void __launch_bounds__(LNT) k_edge_link(LinkArgs a, int cluster_size)
+__global__ void __launch_bounds__(LNT, 2) k_edge_link(LinkArgs a, int cluster_size)
 {
     extern __shared__ uint32_t smem[];
     __shared__ int s_flags[2][8];
