@@ -158,7 +158,10 @@ __global__ void __launch_bounds__(RNT, RUN_CTAS) k_pose_run(PoseArgs a, int roun
 }
 
 // ---- 3. second-pose candidates (RPP::Get2ndPose_Exact), one thread per queued quad --------------
-__global__ void __launch_bounds__(PNT) k_pose_second(PoseArgs a, int round)
+#ifndef SECOND_CTAS
+#define SECOND_CTAS 4  // 128 registers: the spills sit in L1 (no shared memory here) and twice the warps hide the fp64 latency (pose 5.24 -> 4.92 ms per 4096 frames)
+#endif
+__global__ void __launch_bounds__(PNT, SECOND_CTAS) k_pose_second(PoseArgs a, int round)
 {
     const int ntask = a.cnt->n_t1[round];
     const int* list = a.list1 + (size_t)round * a.cap;
@@ -380,7 +383,7 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
     MCHECK(c, cudaFuncSetAttribute(k_pose_run<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, run_smem));
     MCHECK(c, cudaFuncSetAttribute(k_pose_run<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, run_smem));
     k_pose_run<false><<<run_blocks, RNT, run_smem, c->stream>>>(a, 0);
-    k_pose_second<<<flat_blocks, PNT, 0, c->stream>>>(a, 0);
+    k_pose_second<<<c->sm_count * SECOND_CTAS * 2, PNT, 0, c->stream>>>(a, 0);
     k_pose_run<true><<<run_blocks, RNT, run_smem, c->stream>>>(a, 0);
     k_pose_select<<<flat_blocks, PNT, 0, c->stream>>>(a, 0);
     k_pose_cluster<<<n, PNT, 0, c->stream>>>(a);
