@@ -164,7 +164,10 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     static const int chunk_env = []() { const char* e = getenv("MANTIS_CHUNK"); return e ? atoi(e) : 0; }();
     int CHUNK = chunk_env > 0 ? chunk_env : (int)(4096.0 * (640.0 * 480.0) / ((double)W * H));
     if (chunk_env <= 0) CHUNK = CHUNK < 256 ? 256 : CHUNK > 4096 ? 4096 : CHUNK;
-    if (mem == MANTIS_MEM_HOST && chunk_env <= 0 && CHUNK > 1024) CHUNK = 1024;  // finer grain for the copy/compute overlap
+    // Host frames: the step is bound by the H2D copy (3.8 GB per 4096 frames at 640x480), so what counts is that the
+    // kernels of a chunk finish before the next copy does, and that the LAST chunk -- the only one whose kernels are
+    // not hidden -- is short: 512-frame chunks, the final one split once more.
+    if (mem == MANTIS_MEM_HOST && chunk_env <= 0 && CHUNK > 512) CHUNK = 512;
     const int WW = words_per_row(W);
     const int nc_max = n < CHUNK ? n : CHUNK;
     const size_t plane_bytes = (size_t)nc_max * H * WW * sizeof(uint32_t);
@@ -197,8 +200,17 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
             }
         }
     }
+    // chunk boundaries
+    std::vector<int> start;
+    for (int f0 = 0; f0 < n; f0 += CHUNK) {
+        start.push_back(f0);
+        const int nc = (n - f0 < CHUNK) ? (n - f0) : CHUNK;
+        if (mem == MANTIS_MEM_HOST && f0 + CHUNK >= n && f0 > 0 && nc >= 256) start.push_back(f0 + nc / 2);
+    }
+    start.push_back(n);
+    const int n_chunks = (int)start.size() - 1;
     auto issue_copy = [&](int k) -> int {
-        const int f0 = k * CHUNK, nc = (n - f0 < CHUNK) ? (n - f0) : CHUNK, buf = k & 1;
+        const int f0 = start[k], nc = start[k + 1] - f0, buf = k & 1;
         uint8_t* dst = (uint8_t*)(buf ? c->stage_in2.p : c->stage_in.p);
         if (k >= 2) MCHECK(c, cudaStreamWaitEvent(c->copy_stream, c->ev_free[buf], 0));
         if (contiguous) {
@@ -214,14 +226,14 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     if (host && (rc = issue_copy(0))) return rc;
 
     std::vector<pm::Camera> cams((size_t)nc_max);
-    for (int f0 = 0, k = 0; f0 < n; f0 += CHUNK, ++k) {
-        const int nc = (n - f0 < CHUNK) ? (n - f0) : CHUNK;
+    for (int k = 0; k < n_chunks; ++k) {
+        const int f0 = start[k], nc = start[k + 1] - f0;
         const uint8_t* d_in;
         size_t pitch;
         int stride;
         prof_mark(c, 0);
         if (host) {
-            if (f0 + CHUNK < n && (rc = issue_copy(k + 1))) return rc;
+            if (k + 1 < n_chunks && (rc = issue_copy(k + 1))) return rc;
             MCHECK(c, cudaStreamWaitEvent(c->stream, c->ev_copied[k & 1], 0));
             stride = 3 * W;
             pitch = tight;
