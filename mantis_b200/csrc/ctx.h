@@ -50,6 +50,7 @@ struct mantis_ctx {
     int map_planar = 0;                      // every map point has z == 0 (the reference's floor grid)
     DevBuf d_atan;                           // (i pi/256, tan(i pi/256)) table of the fast fp64 atan (search.cu)
     Tf rotz;                                 // +90 degrees about z
+    DevBuf search_ticket;                    // k_search: frame ticket counter of the persistent CTAs
     DevBuf stage_in, stage_in2, stage_out0, stage_out1;  // device staging for MANTIS_MEM_HOST callers
     cudaStream_t copy_stream = nullptr;       // H2D of the next chunk while the current one computes
     cudaEvent_t ev_copied[2] = {}, ev_free[2] = {};

@@ -1,5 +1,5 @@
 // search.cu -- K8/K9/K10: map-correspondence scoring, stochastic refinement, cell shifts and yaw
-// disambiguation; one 1024-thread CTA per frame.
+// disambiguation; persistent 1024-thread CTAs (one per SM), frames handed out through a ticket counter.
 //
 //   evaluateHypotheses / evaluateHypothesis / evaluateHypothesisWithImageWHITE / computePointErrorFAST
 //                                     include/mantis3/HypothesisEvaluation.h:31-41,71-158,218-227
@@ -10,9 +10,12 @@
 //                                     HypothesisEvaluation.h:43-66,89-105,160-266,521-581
 //
 // Scoring is a warp task: 32 map points of one hypothesis are projected in fp64 through the
-// fisheye model, the pixel (cvRound addressing, mask bit) is gathered from the L2-resident frame,
-// and the integer colour error is shuffled down to one shared-memory atomic per warp.  Integer
-// sums make the score independent of evaluation order, so the greedy `<` decisions are exact.
+// fisheye model (branch-free), the pixel (cvRound addressing; mask bit from the frame's mask plane,
+// staged in shared memory when it fits) is gathered from the L2-resident frame, and the integer colour
+// error is reduced to one shared-memory atomic per warp and hypothesis.  Tasks run in blocks of four:
+// projections first, then the block's mask words, then its pixel words (score_loop).  Integer sums
+// make the score independent of evaluation order, so the greedy `<` decisions are exact.  Every scoring
+// phase of a frame goes through one inlined copy of that loop (phase loop in k_search).
 // The Gaussian perturbations of the refinement are a fixed table: the reference draws them from
 // cv::RNG(1), here re-seeded per frame, so they are the same for every frame of a context.
 #include "ctx.h"
@@ -97,15 +100,14 @@ __device__ __forceinline__ PoseXY load_pose(const Tf& c2w)
     p.full = &c2w;
     return p;
 }
-template <bool PLANAR>
-__device__ __forceinline__ bool project(const PoseXY& P, const CamK& cam, double px, double py, double pz,
-                                        const double2* __restrict__ atan_tab, double W, double H, double& u, double& v)
+__device__ __forceinline__ bool project(const PoseXY& P, const CamK& cam, double px, double py, double pz, bool planar,
+                                        const double2* __restrict__ atan_tab, int W, int H, double& u, double& v)
 {
     double c[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         double acc = fma(P.rx[i], px, fma(P.ry[i], py, P.t[i]));
-        if (!PLANAR) acc = fma(P.full->R[i * 3 + 2], pz, acc);  // the map is the floor plane: z = 0 adds nothing
+        if (!planar) acc = fma(P.full->R[i * 3 + 2], pz, acc);  // the map is the floor plane: z = 0 adds nothing
         c[i] = acc;
     }
     if (!(c[2] > 1e-300)) return false;  // behind the camera (the reference's z > 0), or no usable reciprocal
@@ -143,7 +145,9 @@ struct SearchArgs {
     const Tf* rand_tf;  // [iterations * particles]
     const double* shifts;  // [n_shift][2]
     int n_shift, iterations, particles;
-    double Wd, Hd;  // frame size as doubles (the in-frame test compares doubles)
+    double Wd, Hd;
+    unsigned* ticket; int n;
+    int mask_in_smem;  // the frame's mask plane fits behind `Shared` in dynamic shared memory
     Tf rotz;
     double projection_bias, color_bias;
     mantis_result* out;
@@ -151,6 +155,18 @@ struct SearchArgs {
     long long* dbg;             // tuning aid: clock64 per phase (null = off)
 };
 
+// What the scoring loop needs about the frame, in shared memory: every use is one broadcast LDS, which is
+// cheaper than recomputing it from blockIdx or holding it in one of 64 registers.
+struct ScoreFrame {
+    double2 fcx, fcy;         // (fx, cx), (fy, cy)
+    double D0, D1, D2, D3;
+};
+
+struct Gather {  // per frame: where the masked image lives
+    const uint8_t* bgr_al;    // frame base rounded down to 4 bytes
+    const uint32_t* mask;     // generic pointer: the copy of the frame's mask plane in shared memory when it fits, else global
+    unsigned delta;           // frame base - bgr_al
+};
 struct Shared {
     double map_x[MAX_MAP], map_y[MAX_MAP], map_z[MAX_MAP];
     double2 atan_tab[ATAN_N];
@@ -160,6 +176,10 @@ struct Shared {
     Tf cand_w2c[96], cand_c2w[96];
     Hyp best;
     Img img;  // per-frame image descriptor: kept here so that the base pointers are one broadcast load away
+    ScoreFrame sf;
+    Gather gat;
+    int frame;
+    double2 wpose[NWARP][8];  // per-warp staging of the current hypothesis: (rx,ry) x3, (t0,t1), (t2,-), (rz0,rz1), (rz2,-)
     unsigned int green_acc[80 * 40];  // integer colour error summed over the 10x10 window
     int green_xy[80 * 40];            // cvRound(u) | cvRound(v) << 16 of the projected point, -1 if not in frame
     unsigned char green_half[80 * 40];  // u or v exactly on a .5: per-pixel rounding differs from a shifted window
@@ -167,92 +187,181 @@ struct Shared {
     short top20[20];
 };
 
-// score `nh` hypotheses (c2w via the accessor) against all map points on the masked image.
-// The (hypothesis, 32-point chunk) tasks are cut into one contiguous range per warp, so a warp
-// reduces and publishes once per hypothesis it touches instead of once per chunk.
-template <bool PLANAR, class GetC2W>
-__device__ void score_white(Shared& s, const Img& im, const CamK& cam, int n_map, double Wd, double Hd, int nh, double bias,
-                            GetC2W get)
+// Branch-free projection (same operations, in the same order, as project()): every lane runs the whole
+// chain and carries a validity predicate, so the projections of a block form straight-line code.  Garbage in (a point behind the camera) stays garbage and ends with ok = false.
+template <bool PLANAR, bool DIST>
+__device__ __forceinline__ bool project_bf(const double2* __restrict__ wp, const ScoreFrame& cam, double px, double py, double pz,
+                                           const double2* __restrict__ tab, double Wd, double Hd, double& u, double& v)
+{
+    double c[3];
+    {
+        const double2 r0 = wp[0], r1 = wp[1], r2_ = wp[2], t01 = wp[3], t2 = wp[4];
+        c[0] = fma(r0.x, px, fma(r0.y, py, t01.x));
+        c[1] = fma(r1.x, px, fma(r1.y, py, t01.y));
+        c[2] = fma(r2_.x, px, fma(r2_.y, py, t2.x));
+        if (!PLANAR) {
+            const double2 z01 = wp[5], z2 = wp[6];
+            c[0] = fma(z01.x, pz, c[0]); c[1] = fma(z01.y, pz, c[1]); c[2] = fma(z2.x, pz, c[2]);
+        }
+    }
+    bool ok = c[2] > 1e-300;
+    const double iz = fast_rcp(c[2]);
+    const double x = c[0] * iz, y = c[1] * iz;
+    const double r2 = fma(x, x, y * y);
+    const bool mid = r2 > 1e-16 && r2 < 1e300;
+    ok = ok && r2 < 1e300;  // also drops NaN
+    const double inv_r = fast_rsqrt(r2), r = r2 * inv_r;
+    // fast_atan_pos with an index that is safe for garbage input
+    const bool big = r > 1.0;
+    const float q = (float)(big ? inv_r : r);
+    float est = q * fmaf(0.273f, 1.0f - q, 0.78539816f);
+    if (big) est = 1.57079633f - est;
+    const unsigned ti = min((unsigned)__float2int_rn(est * 81.48733086305041f), (unsigned)(ATAN_N - 1));
+    const double2 e = tab[ti];
+    const double ax = (r - e.y) * fast_rcp(fma(r, e.y, 1.0));
+    const double ax2 = ax * ax;
+    const double ap = fma(ax2, fma(ax2, fma(ax2, -1.0 / 7.0, 0.2), -1.0 / 3.0), 1.0);
+    const double theta = fma(ax, ap, e.x);
+    double theta_d = theta;
+    if (DIST) {
+        const double t2 = theta * theta;
+        theta_d = theta * fma(t2, fma(t2, fma(t2, fma(t2, cam.D3, cam.D2), cam.D1), cam.D0), 1.0);
+    }
+    const double cdist = mid ? theta_d * inv_r : 1.0;
+    const double2 fcx = cam.fcx, fcy = cam.fcy;  // late broadcast loads instead of eight live registers
+    u = fma(x * cdist, fcx.x, fcx.y);
+    v = fma(y * cdist, fcy.x, fcy.y);
+    return ok && u < Wd && v < Hd && u >= 0 && v > 0;
+}
+
+// x == W or y == H (the reference addresses pixel y*W + x unchecked): a few points per frame, kept out of line
+__device__ __noinline__ void rare_point(Shared& s, int h, int x, int y)
+{
+    const int er = pixel_err(s.img, x, y, true, 255, 255, 255);
+    if (er) atomicAdd(&s.sum[h], (unsigned long long)er);
+}
+
+// Score `nh` hypotheses against all map points on the masked image.  The c2w of hypothesis h is the Tf at
+// tf_base + (sel ? sel[h] : h) * tf_stride (global or shared memory).
+//
+// A warp task is (hypothesis, 32 map points), projected in fp64, branch-free.  Tasks are cut into one contiguous
+// range per warp and run in blocks of up to BLK tasks of one hypothesis: first the projections, then the mask
+// words of the whole block, then its pixel words, then the colour errors.  The gathers of a block are
+// independent of each other, so their latencies overlap without a software pipeline carried in registers.
+// err = sum (255 - c)^2 is one IDP.4A on the complemented pixel.
+template <bool PLANAR, bool DIST>
+__device__ __forceinline__ void score_loop(Shared& s, const SearchArgs& a, int nh, const char* tf_base, int tf_stride,
+                                           const short* sel)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < nh; i += SNT) { s.sum[i] = 0ull; s.cnt[i] = 0; }
-    __syncthreads();
+    const int n_map = a.n_map;
     const int chunks = (n_map + 31) >> 5;
     const int total = nh * chunks, per = (total + NWARP - 1) / NWARP;
     const int t_begin = min(warp * per, total), t_end = min(t_begin + per, total);
     int h = t_begin / chunks, ch = t_begin - h * chunks;
-    int e_acc = 0, ok_acc = 0;
-    PoseXY c2w;
-    if (t_begin < t_end) c2w = load_pose(get(h));
-    // Three-stage software pipeline over the tasks of this warp, so that the two dependent gathers of a
-    // point (mask word, then pixel bytes) are in flight while the next points are being projected:
-    //   stage 1 (task t)    project, issue the mask-word load
-    //   stage 2 (task t-1)  test the mask bit, issue the pixel loads
-    //   stage 3 (task t-2)  add the colour error
-    uint32_t m_word = 0;
-    int m_key = -1;  // (pixel byte offset << 5) | mask bit, -1 = nothing pending
-    // pixel in flight: the two aligned words that hold its three bytes, and the byte shift.  All ones = white =
-    // no contribution; err = sum (255 - c)^2 is one IDP.4A on the complemented pixel.
-    uint32_t w0 = ~0u, w1 = ~0u, sh8 = 0u;
-    auto stage3 = [&]() {
-        const uint32_t inv = ~__funnelshift_r(w0, w1, sh8) & 0xffffffu;
-        e_acc = (int)__dp4a(inv, inv, (uint32_t)e_acc);
-        w0 = w1 = ~0u;
+    unsigned e_acc = 0;
+    int ok_acc = 0;
+    const uint8_t* const bgr_al = s.gat.bgr_al;
+    const uint32_t* const mask = s.gat.mask;
+    const unsigned delta = s.gat.delta;
+    // The pose of the current hypothesis is staged in a per-warp shared-memory slot and re-read (broadcast) by
+    // every task: nine doubles held in registers would spill.
+    double2* const wp = s.wpose[warp];
+    auto load_tf = [&](int hh) {
+        const Tf* tf = reinterpret_cast<const Tf*>(tf_base + (size_t)(sel ? (int)sel[hh] : hh) * tf_stride);
+        __syncwarp();
+        if (lane < 3) wp[lane] = make_double2(tf->R[lane * 3], tf->R[lane * 3 + 1]);
+        else if (lane == 3) wp[3] = make_double2(tf->t[0], tf->t[1]);
+        else if (lane == 4) wp[4] = make_double2(tf->t[2], 0.0);
+        else if (!PLANAR && lane == 5) wp[5] = make_double2(tf->R[2], tf->R[5]);
+        else if (!PLANAR && lane == 6) wp[6] = make_double2(tf->R[8], 0.0);
+        __syncwarp();
     };
-    auto stage2 = [&]() {
-        if (m_key >= 0) {
-            w0 = w1 = 0u;  // masked out = black
-            if ((m_word >> (m_key & 31)) & 1u) {
-                const uintptr_t p = (uintptr_t)im.bgr + ((unsigned)m_key >> 5);
-                const uint32_t* q = reinterpret_cast<const uint32_t*>(p & ~(uintptr_t)3);
-                sh8 = ((unsigned)p & 3u) << 3;
-                w0 = __ldg(q);
-                if (sh8 >= 16u) w1 = __ldg(q + 1);  // the third byte sits in the next word
-            }
-            m_key = -1;
-        }
-    };
-    for (int t = t_begin; t < t_end; ++t) {
-        stage3();
-        stage2();
-        const int pi = ch * 32 + lane;
-        if (pi < n_map) {
+    if (t_begin < t_end) load_tf(h);
+#ifndef SEARCH_BLK
+#define SEARCH_BLK 4
+#endif
+    constexpr int BLK = SEARCH_BLK;
+    constexpr unsigned NONE = 0xffffffffu;
+    const int W = a.W, H = a.H;
+    for (int t = t_begin; t < t_end;) {
+        const int nb = min(BLK, min(chunks - ch, t_end - t));  // warp-uniform
+        unsigned key[BLK];  // (y << 16) | x of an in-frame point
+#pragma unroll
+        for (int b = 0; b < BLK; ++b) {
+            key[b] = NONE;
+            if (b >= nb) continue;
+            const int pi = (ch + b) * 32 + lane;
+            const int pim = min(pi, n_map - 1);
             double u, v;
-            if (project<PLANAR>(c2w, cam, s.map_x[pi], s.map_y[pi], PLANAR ? 0.0 : s.map_z[pi], s.atan_tab, Wd, Hd, u, v)) {
-                ++ok_acc;
-                const int x = __double2int_rn(u), y = __double2int_rn(v);
-                const unsigned off = (unsigned)(y * im.stride + 3 * x);
-                if ((unsigned)x < (unsigned)im.W && (unsigned)y < (unsigned)im.H && off < (1u << 26)) {
-                    m_word = __ldg(im.mask + (unsigned)(y * im.WW + (x >> 5)));
-                    m_key = (int)(off << 5) | (x & 31);
-                } else {  // x == W or y == H (the reference's linear addressing), or a frame beyond 64 MB
-                    e_acc += pixel_err(im, x, y, true, 255, 255, 255);  // x == W or y == H: the reference's linear addressing
-                }
+            bool ok = project_bf<PLANAR, DIST>(wp, s.sf, s.map_x[pim], s.map_y[pim], PLANAR ? 0.0 : s.map_z[pim], s.atan_tab,
+                                               a.Wd, a.Hd, u, v);
+            ok = ok && pi < n_map;
+            const int x = __double2int_rn(u), y = __double2int_rn(v);  // ok implies x >= 0, y >= 0
+            const bool inside = ok && x < W && y < H;
+            ok_acc += ok ? 1 : 0;
+            if (inside) key[b] = ((unsigned)y << 16) | (unsigned)x;
+            if (ok && !inside) {  // x == W or y == H: the reference's linear addressing
+                rare_point(s, h, x, y);
             }
         }
-        if (++ch == chunks || t + 1 == t_end) {
-            stage3(); stage2(); stage3();  // drain: everything pending belongs to hypothesis h
-            const int e = __reduce_add_sync(0xffffffffu, e_acc), ok = __reduce_add_sync(0xffffffffu, ok_acc);
-            if (lane == 0 && ok) {
-                atomicAdd(&s.sum[h], (unsigned long long)e);
-                atomicAdd(&s.cnt[h], ok);
+        // the mask words of the block
+        uint32_t mw[BLK];
+#pragma unroll
+        for (int b = 0; b < BLK; ++b) {
+            const unsigned k = key[b];
+            mw[b] = 0u;
+            if (k != NONE) mw[b] = mask[(k >> 16) * (unsigned)a.WW + ((k & 0xffffu) >> 5)] >> (k & 31u);
+        }
+        // the pixel words: all ones = no contribution, zero = masked out = black
+        uint32_t w0[BLK], w1[BLK], sh8[BLK];
+#pragma unroll
+        for (int b = 0; b < BLK; ++b) {
+            const unsigned k = key[b];
+            const unsigned o = (k >> 16) * (unsigned)a.stride + 3u * (k & 0xffffu) + delta;
+            w0[b] = w1[b] = k != NONE ? 0u : ~0u;
+            sh8[b] = (o & 3u) << 3;
+            const bool on = k != NONE && (mw[b] & 1u);
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(bgr_al + (o & ~3u));
+            if (on) w0[b] = __ldg(p);
+            if (on && (o & 2u)) w1[b] = __ldg(p + 1);
+        }
+#pragma unroll
+        for (int b = 0; b < BLK; ++b) {
+            const uint32_t inv = ~__funnelshift_r(w0[b], w1[b], sh8[b]) & 0xffffffu;
+            e_acc = __dp4a(inv, inv, e_acc);
+        }
+        ch += nb; t += nb;
+        if (ch == chunks || t == t_end) {
+            const unsigned e = __reduce_add_sync(0xffffffffu, e_acc);
+            const int okw = __reduce_add_sync(0xffffffffu, ok_acc);
+            if (lane == 0 && okw) {
+                atomicAdd(&s.cnt[h], okw);
+                if (e) atomicAdd(&s.sum[h], (unsigned long long)e);
             }
             e_acc = 0; ok_acc = 0;
-            if (ch == chunks) { ch = 0; ++h; if (t + 1 < t_end) c2w = load_pose(get(h)); }
+            if (ch == chunks) { ch = 0; ++h; if (t < t_end) load_tf(h); }
         }
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < nh; i += SNT)
-        s.err[i] = s.cnt[i] > 0 ? (double)s.sum[i] / ((double)s.cnt[i] * bias) : DBLMAX;
-    __syncthreads();
 }
 
-template <bool PLANAR>
-__global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
+__global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Shared& s = *reinterpret_cast<Shared*>(smem_raw);
-    const int frame = blockIdx.x, tid = threadIdx.x;
+    const int tid = threadIdx.x;
+    // map and atan table: once per CTA
+    for (int i = tid; i < a.n_map; i += SNT) {
+        s.map_x[i] = a.map[3 * i]; s.map_y[i] = a.map[3 * i + 1]; s.map_z[i] = a.map[3 * i + 2];
+    }
+    for (int i = tid; i < ATAN_N; i += SNT) s.atan_tab[i] = a.atan_tab[i];
+    // persistent CTA: frames are handed out through a ticket counter
+    for (;;) {
+    __syncthreads();  // the previous frame is done with shared memory
+    if (tid == 0) s.frame = (int)atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    const int frame = s.frame;
+    if (frame >= a.n) break;
     mantis_result* out = a.out + frame;
     mantis_frame_trace* tr = a.trace ? a.trace + frame : nullptr;
     const FrameQuads* fq = a.quads + frame;
@@ -275,7 +384,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
             tr->best_rot = -1; tr->pad_ = 0;
         }
     }
-    if (fq->flags || fq->n_quads == 0 || n_sel == 0) return;
+    if (fq->flags || fq->n_quads == 0 || n_sel == 0) continue;
 
     if (tid == 0) {
         s.img.bgr = a.bgr + (size_t)frame * a.pitch;
@@ -290,82 +399,119 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
         cam.D0 = c0.D[0]; cam.D1 = c0.D[1]; cam.D2 = c0.D[2]; cam.D3 = c0.D[3];
         cam.has_dist = c0.D[0] != 0 || c0.D[1] != 0 || c0.D[2] != 0 || c0.D[3] != 0;
     }
+    const bool planar = a.map_planar != 0;
+    if (tid == 32) {
+        ScoreFrame& k = s.sf;
+        k.fcx = make_double2(cam.fx, cam.cx); k.fcy = make_double2(cam.fy, cam.cy);
+        k.D0 = cam.D0; k.D1 = cam.D1; k.D2 = cam.D2; k.D3 = cam.D3;
+    }
     const Hyp* hyps = a.hyps + (size_t)frame * MANTIS_MAX_HYPS;
     const short* sel = a.sel + (size_t)frame * MANTIS_MAX_HYPS;
-    for (int i = tid; i < a.n_map; i += SNT) {
-        s.map_x[i] = a.map[3 * i]; s.map_y[i] = a.map[3 * i + 1]; s.map_z[i] = a.map[3 * i + 2];
+    if (a.mask_in_smem) {
+        // The mask plane is gathered once per (hypothesis, point) at 32 unrelated addresses per warp: from global
+        // memory that is 32 L1 tag lookups per instruction and the scoring loop ends up bound by the LSU; from
+        // shared memory it is a handful of bank conflicts.
+        uint32_t* sm = reinterpret_cast<uint32_t*>(smem_raw + sizeof(Shared));
+        const uint32_t* gm = a.mask_bits + (size_t)frame * a.H * a.WW;
+        for (int i = tid; i < a.H * a.WW; i += SNT) sm[i] = __ldg(gm + i);
     }
-    for (int i = tid; i < ATAN_N; i += SNT) s.atan_tab[i] = a.atan_tab[i];
-    __syncthreads();
+    if (tid == 64) {
+        const uint8_t* base = a.bgr + (size_t)frame * a.pitch;
+        s.gat.delta = (unsigned)((uintptr_t)base & 3u);
+        s.gat.bgr_al = base - s.gat.delta;
+        s.gat.mask = a.mask_in_smem ? reinterpret_cast<const uint32_t*>(smem_raw + sizeof(Shared))
+                                    : a.mask_bits + (size_t)frame * a.H * a.WW;
+    }
     long long tk = clock64();
     auto tick = [&](int slot) {
         if (a.dbg && tid == 0) { long long t = clock64(); atomicAdd((unsigned long long*)&a.dbg[slot], (unsigned long long)(t - tk)); tk = t; }
     };
 
-    // (6) evaluateHypotheses on the kept cluster, (7) best 1
-    score_white<PLANAR>(s, im, cam, a.n_map, a.Wd, a.Hd, n_sel, a.projection_bias, [&](int h) -> const Tf& { return hyps[sel[h]].c2w; });
-    if (tid == 0) {
-        int bi = 0;  // stable descending sort, last element: minimal error, highest index among ties
-        for (int i = 1; i < n_sel; ++i)
-            if (s.err[i] <= s.err[bi]) bi = i;
-        s.best = hyps[sel[bi]];
-        s.best.error = s.err[bi];
-        if (tr) tr->first_best_error = s.err[bi];
-    }
-    __syncthreads();
-
-    tick(0);
-    // (8) optimizeHypothesisWithParticleFilter
-    for (int it = 0; it < a.iterations; ++it) {
-        if (tid < a.particles) {
-            pm::tf_mul(s.best.w2c, a.rand_tf[it * a.particles + tid], s.cand_w2c[tid]);
-            pm::tf_inv(s.cand_w2c[tid], s.cand_c2w[tid]);
+    // Phases of the search, all through ONE inlined copy of the scoring loop:
+    //   0                 (6) evaluateHypotheses on the kept cluster, (7) best 1
+    //   1 .. iterations   (8) optimizeHypothesisWithParticleFilter
+    //   iterations + 1    (9) the 81 cell shifts, (10) evaluate, (11) best 20
+    const int ns = a.n_shift;
+    const int keep = ns < 20 ? ns : 20;
+    const int mode = (planar ? 2 : 0) | (cam.has_dist ? 1 : 0);  // uniform over the CTA
+    for (int ph = 0; ph <= a.iterations + 1; ++ph) {
+        int nh;
+        const char* tf_base = reinterpret_cast<const char*>(s.cand_c2w);
+        int tf_stride = (int)sizeof(Tf);
+        const short* selp = nullptr;
+        if (ph == 0) {
+            nh = n_sel; tf_base = reinterpret_cast<const char*>(&hyps[0].c2w); tf_stride = (int)sizeof(Hyp); selp = sel;
+        } else if (ph <= a.iterations) {
+            nh = a.particles;
+            if (tid < nh) {
+                pm::tf_mul(s.best.w2c, a.rand_tf[(ph - 1) * a.particles + tid], s.cand_w2c[tid]);
+                pm::tf_inv(s.cand_w2c[tid], s.cand_c2w[tid]);
+            }
+        } else {
+            nh = ns;
+            if (tid < ns) {
+                Tf w = s.best.w2c;
+                w.t[0] += a.shifts[2 * tid];
+                w.t[1] += a.shifts[2 * tid + 1];
+                w.t[2] += 0;
+                s.cand_w2c[tid] = w;
+                pm::tf_inv(w, s.cand_c2w[tid]);
+            }
         }
+        for (int i = tid; i < nh; i += SNT) { s.sum[i] = 0ull; s.cnt[i] = 0; }
         __syncthreads();
-        score_white<PLANAR>(s, im, cam, a.n_map, a.Wd, a.Hd, a.particles, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
-        if (tid == 0) {
-            int bp = -1;
-            double be = s.best.error;
-            for (int p = 0; p < a.particles; ++p)
-                if (s.err[p] < be) { be = s.err[p]; bp = p; }
-            if (bp >= 0) {
-                s.best.w2c = s.cand_w2c[bp];
-                s.best.c2w = s.cand_c2w[bp];
-                s.best.error = be;
+        if (mode == 2) score_loop<true, false>(s, a, nh, tf_base, tf_stride, selp);
+        else if (mode == 3) score_loop<true, true>(s, a, nh, tf_base, tf_stride, selp);
+        else if (mode == 0) score_loop<false, false>(s, a, nh, tf_base, tf_stride, selp);
+        else score_loop<false, true>(s, a, nh, tf_base, tf_stride, selp);
+        __syncthreads();
+        __syncthreads();
+        for (int i = tid; i < nh; i += SNT)
+            s.err[i] = s.cnt[i] > 0 ? (double)s.sum[i] / ((double)s.cnt[i] * a.projection_bias) : DBLMAX;
+        __syncthreads();
+        if (ph == 0) {
+            if (tid == 0) {
+                int bi = 0;  // stable descending sort, last element: minimal error, highest index among ties
+                for (int i = 1; i < n_sel; ++i)
+                    if (s.err[i] <= s.err[bi]) bi = i;
+                s.best = hyps[sel[bi]];
+                s.best.error = s.err[bi];
+                if (tr) tr->first_best_error = s.err[bi];
+            }
+            tick(0);
+        } else if (ph <= a.iterations) {
+            if (tid == 0) {
+                int bp = -1;
+                double be = s.best.error;
+                for (int p = 0; p < a.particles; ++p)
+                    if (s.err[p] < be) { be = s.err[p]; bp = p; }
+                if (bp >= 0) {
+                    s.best.w2c = s.cand_w2c[bp];
+                    s.best.c2w = s.cand_c2w[bp];
+                    s.best.error = be;
+                }
+            }
+        } else {
+            if (tr)
+                for (int i = tid; i < ns && i < 81; i += SNT) tr->shift_err[i] = s.err[i];
+            // (11) best 20: position in a stable descending sort; keep the last 20
+            if (tid < ns) {
+                int pos = 0;
+                const double e = s.err[tid];
+                for (int j = 0; j < ns; ++j) pos += (s.err[j] > e) || (s.err[j] == e && j < tid);
+                if (pos >= ns - keep) s.top20[pos - (ns - keep)] = (short)tid;
             }
         }
         __syncthreads();
+        if (ph == a.iterations) {  // also when iterations == 0: the refined pose is the first best
+            if (tid == 0 && tr) {
+                tr->optimized_error = s.best.error;
+                for (int k = 0; k < 9; ++k) tr->optimized_w2c[k] = s.best.w2c.R[k];
+                for (int k = 0; k < 3; ++k) tr->optimized_w2c[9 + k] = s.best.w2c.t[k];
+            }
+            tick(1);
+        }
     }
-    if (tid == 0 && tr) {
-        tr->optimized_error = s.best.error;
-        for (int k = 0; k < 9; ++k) tr->optimized_w2c[k] = s.best.w2c.R[k];
-        for (int k = 0; k < 3; ++k) tr->optimized_w2c[9 + k] = s.best.w2c.t[k];
-    }
-
-    tick(1);
-    // (9) the 81 cell shifts, (10) evaluate
-    const int ns = a.n_shift;
-    if (tid < ns) {
-        Tf w = s.best.w2c;
-        w.t[0] += a.shifts[2 * tid];
-        w.t[1] += a.shifts[2 * tid + 1];
-        w.t[2] += 0;
-        s.cand_w2c[tid] = w;
-        pm::tf_inv(w, s.cand_c2w[tid]);
-    }
-    __syncthreads();
-    score_white<PLANAR>(s, im, cam, a.n_map, a.Wd, a.Hd, ns, a.projection_bias, [&](int h) -> const Tf& { return s.cand_c2w[h]; });
-    if (tr)
-        for (int i = tid; i < ns && i < 81; i += SNT) tr->shift_err[i] = s.err[i];
-    // (11) best 20: position in a stable descending sort; keep the last 20
-    const int keep = ns < 20 ? ns : 20;
-    if (tid < ns) {
-        int pos = 0;
-        const double e = s.err[tid];
-        for (int j = 0; j < ns; ++j) pos += (s.err[j] > e) || (s.err[j] == e && j < tid);
-        if (pos >= ns - keep) s.top20[pos - (ns - keep)] = (short)tid;
-    }
-    __syncthreads();
 
     tick(2);
     // (12) determineBestYaw on the original image: 4 rotations x `keep` hypotheses x green points
@@ -386,7 +532,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
     for (int item = tid; item < nrot * ng; item += SNT) {
         const int h = item / ng, gi = item - h * ng, mi = a.n_green_off + gi;
         double u, v;
-        const bool ok = project<PLANAR>(load_pose(s_rot_c2w[h]), cam, s.map_x[mi], s.map_y[mi], s.map_z[mi], s.atan_tab, a.Wd, a.Hd, u, v);
+        const bool ok = project(load_pose(s_rot_c2w[h]), cam, s.map_x[mi], s.map_y[mi], s.map_z[mi], planar, s.atan_tab, im.W, im.H, u, v);
         const int slot = h * 40 + gi;
         s.green_acc[slot] = 0;
         s.green_xy[slot] = ok ? ((__double2int_rn(u) & 0xffff) | (__double2int_rn(v) << 16)) : -1;
@@ -462,6 +608,7 @@ __global__ void __launch_bounds__(SNT) k_search(SearchArgs a)
             out->error = s.hyp_err[best * keep + keep - 1];
         }
     }
+    }  // frame loop
 }
 
 }  // namespace
@@ -492,14 +639,23 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
     a.color_bias = c->cfg.color_projection_bias;
     a.out = d_out; a.trace = d_trace;
     a.dbg = (long long*)c->dbg_clocks;
-    const size_t smem = sizeof(Shared);
-    if (c->map_planar) {
-        MCHECK(c, cudaFuncSetAttribute(k_search<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_search<true><<<n, SNT, smem, c->stream>>>(a);
-    } else {
-        MCHECK(c, cudaFuncSetAttribute(k_search<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_search<false><<<n, SNT, smem, c->stream>>>(a);
+    // persistent CTAs (one per SM); frames come from a ticket counter
+    const int grid = n < c->sm_count ? n : c->sm_count;
+    int rc = ctx_reserve(c, c->search_ticket, sizeof(unsigned));
+    if (rc) return rc;
+    a.ticket = (unsigned*)c->search_ticket.p;
+    a.n = n;
+    MCHECK(c, cudaMemsetAsync(a.ticket, 0, sizeof(unsigned), c->stream));
+    size_t smem = sizeof(Shared);
+    {
+        cudaFuncAttributes fa;
+        MCHECK(c, cudaFuncGetAttributes(&fa, k_search));
+        const size_t room = 227 * 1024 - fa.sharedSizeBytes - 1024, plane = (size_t)h * a.WW * sizeof(uint32_t);
+        a.mask_in_smem = smem + plane <= room;
+        if (a.mask_in_smem) smem += plane;
     }
+    MCHECK(c, cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_search<<<grid, SNT, smem, c->stream>>>(a);
     c->launches++;
     MCHECK(c, cudaGetLastError());
     return MANTIS_OK;
