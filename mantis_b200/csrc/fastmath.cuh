@@ -35,3 +35,19 @@ __device__ __forceinline__ double fast_rsqrt(double x)  // x normal and finite
     e = fma(-(x * r), r, 1.0);
     return fma(0.5 * r, e, r);
 }
+
+// Cubic-step variants (one instruction fewer / three fewer), used by the projection of search.cu.
+__device__ __forceinline__ double fast_rcp3(double z)  // z normal and finite
+{
+    // y (1 + e + e^2) with e = 1 - z y; e ~ 2^-23, so the result is good to e^3 ~ 2^-69
+    const double y = rcp_seed(z);
+    const double e = fma(-z, y, 1.0);
+    return fma(y, fma(e, e, e), y);
+}
+__device__ __forceinline__ double fast_rsqrt3(double x)  // x normal and finite
+{
+    // r (1 + e/2 + 3 e^2 / 8) with e = 1 - x r^2; e ~ 2^-21, so the result is good to ~ 2^-64
+    const double r = rsqrt_seed(x);
+    const double e = fma(-(x * r), r, 1.0);
+    return fma(r, fma(e, 0.375, 0.5) * e, r);
+}

@@ -46,7 +46,7 @@ __device__ __forceinline__ double fast_atan_pos(double r, double inv_r, const do
     if (big) est = 1.57079633f - est;
     const int i = min(__float2int_rn(est * 81.48733086305041f), ATAN_N - 1);  // 256/pi
     const double2 e = tab[i];
-    const double x = (r - e.y) * fast_rcp(fma(r, e.y, 1.0));
+    const double x = (r - e.y) * fast_rcp3(fma(r, e.y, 1.0));
     const double x2 = x * x;
     const double p = fma(x2, fma(x2, fma(x2, -1.0 / 7.0, 0.2), -1.0 / 3.0), 1.0);
     return fma(x, p, e.x);
@@ -111,12 +111,12 @@ __device__ __forceinline__ bool project(const PoseXY& P, const CamK& cam, double
         c[i] = acc;
     }
     if (!(c[2] > 1e-300)) return false;  // behind the camera (the reference's z > 0), or no usable reciprocal
-    const double iz = fast_rcp(c[2]);
+    const double iz = fast_rcp3(c[2]);
     const double x = c[0] * iz, y = c[1] * iz;
     const double r2 = fma(x, x, y * y);
     double cdist = 1;
     if (r2 > 1e-16 && r2 < 1e300) {  // r > 1e-8
-        const double inv_r = fast_rsqrt(r2), r = r2 * inv_r;
+        const double inv_r = fast_rsqrt3(r2), r = r2 * inv_r;
         const double theta = fast_atan_pos(r, inv_r, atan_tab);
         double theta_d = theta;
         if (cam.has_dist) {
@@ -205,12 +205,12 @@ __device__ __forceinline__ bool project_bf(const double2* __restrict__ wp, const
         }
     }
     bool ok = c[2] > 1e-300;
-    const double iz = fast_rcp(c[2]);
+    const double iz = fast_rcp3(c[2]);
     const double x = c[0] * iz, y = c[1] * iz;
     const double r2 = fma(x, x, y * y);
     const bool mid = r2 > 1e-16 && r2 < 1e300;
     ok = ok && r2 < 1e300;  // also drops NaN
-    const double inv_r = fast_rsqrt(r2), r = r2 * inv_r;
+    const double inv_r = fast_rsqrt3(r2), r = r2 * inv_r;
     // fast_atan_pos with an index that is safe for garbage input
     const bool big = r > 1.0;
     const float q = (float)(big ? inv_r : r);
@@ -218,7 +218,7 @@ __device__ __forceinline__ bool project_bf(const double2* __restrict__ wp, const
     if (big) est = 1.57079633f - est;
     const unsigned ti = min((unsigned)__float2int_rn(est * 81.48733086305041f), (unsigned)(ATAN_N - 1));
     const double2 e = tab[ti];
-    const double ax = (r - e.y) * fast_rcp(fma(r, e.y, 1.0));
+    const double ax = (r - e.y) * fast_rcp3(fma(r, e.y, 1.0));
     const double ax2 = ax * ax;
     const double ap = fma(ax2, fma(ax2, fma(ax2, -1.0 / 7.0, 0.2), -1.0 / 3.0), 1.0);
     const double theta = fma(ax, ap, e.x);
@@ -292,9 +292,8 @@ __device__ __forceinline__ void score_loop(Shared& s, const SearchArgs& a, int n
             key[b] = NONE;
             if (b >= nb) continue;
             const int pi = (ch + b) * 32 + lane;
-            const int pim = min(pi, n_map - 1);
-            double u, v;
-            bool ok = project_bf<PLANAR, DIST>(wp, s.sf, s.map_x[pim], s.map_y[pim], PLANAR ? 0.0 : s.map_z[pim], s.atan_tab,
+            double u, v;  // (the map arrays are zero beyond n_map: no clamp of pi)
+            bool ok = project_bf<PLANAR, DIST>(wp, s.sf, s.map_x[pi], s.map_y[pi], PLANAR ? 0.0 : s.map_z[pi], s.atan_tab,
                                                a.Wd, a.Hd, u, v);
             ok = ok && pi < n_map;
             const int x = __double2int_rn(u), y = __double2int_rn(v);  // ok implies x >= 0, y >= 0
@@ -354,6 +353,7 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
     for (int i = tid; i < a.n_map; i += SNT) {
         s.map_x[i] = a.map[3 * i]; s.map_y[i] = a.map[3 * i + 1]; s.map_z[i] = a.map[3 * i + 2];
     }
+    for (int i = a.n_map + tid; i < MAX_MAP; i += SNT) { s.map_x[i] = 0; s.map_y[i] = 0; s.map_z[i] = 0; }
     for (int i = tid; i < ATAN_N; i += SNT) s.atan_tab[i] = a.atan_tab[i];
     // persistent CTA: frames are handed out through a ticket counter
     for (;;) {
