@@ -187,6 +187,10 @@ struct Shared {
     short top20[20];
 };
 
+// fp64 constants of the projection whose low word is not zero: as literals ptxas rebuilds each of them with
+// two UMOVs at every use (12 issue slots per point); from the constant bank they are direct operands.
+__constant__ double KC[6] = {1e-300, 1e-16, 1e300, -1.0 / 7.0, 0.2, -1.0 / 3.0};
+
 // Branch-free projection (same operations, in the same order, as project()): every lane runs the whole
 // chain and carries a validity predicate, so the projections of a block form straight-line code.  Garbage in (a point behind the camera) stays garbage and ends with ok = false.
 template <bool PLANAR, bool DIST>
@@ -204,12 +208,12 @@ __device__ __forceinline__ bool project_bf(const double2* __restrict__ wp, const
             c[0] = fma(z01.x, pz, c[0]); c[1] = fma(z01.y, pz, c[1]); c[2] = fma(z2.x, pz, c[2]);
         }
     }
-    bool ok = c[2] > 1e-300;
+    bool ok = c[2] > KC[0];
     const double iz = fast_rcp3(c[2]);
     const double x = c[0] * iz, y = c[1] * iz;
     const double r2 = fma(x, x, y * y);
-    const bool mid = r2 > 1e-16 && r2 < 1e300;
-    ok = ok && r2 < 1e300;  // also drops NaN
+    const bool mid = r2 > KC[1] && r2 < KC[2];
+    ok = ok && r2 < KC[2];  // also drops NaN
     const double inv_r = fast_rsqrt3(r2), r = r2 * inv_r;
     // fast_atan_pos with an index that is safe for garbage input
     const bool big = r > 1.0;
@@ -220,7 +224,7 @@ __device__ __forceinline__ bool project_bf(const double2* __restrict__ wp, const
     const double2 e = tab[ti];
     const double ax = (r - e.y) * fast_rcp3(fma(r, e.y, 1.0));
     const double ax2 = ax * ax;
-    const double ap = fma(ax2, fma(ax2, fma(ax2, -1.0 / 7.0, 0.2), -1.0 / 3.0), 1.0);
+    const double ap = fma(ax2, fma(ax2, fma(ax2, KC[3], KC[4]), KC[5]), 1.0);
     const double theta = fma(ax, ap, e.x);
     double theta_d = theta;
     if (DIST) {
