@@ -469,9 +469,44 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
         else if (mode == 0) score_loop<false, false>(s, a, nh, tf_base, tf_stride, selp);
         else score_loop<false, true>(s, a, nh, tf_base, tf_stride, selp);
         __syncthreads();
-        __syncthreads();
-        for (int i = tid; i < nh; i += SNT)
-            s.err[i] = s.cnt[i] > 0 ? (double)s.sum[i] / ((double)s.cnt[i] * a.projection_bias) : DBLMAX;
+        auto err_of = [&](int i) {
+            return s.cnt[i] > 0 ? (double)s.sum[i] / ((double)s.cnt[i] * a.projection_bias) : DBLMAX;
+        };
+        if (ph >= 1 && ph <= a.iterations) {
+            // (8) the greedy update of one refinement iteration, by warp 0: the first particle (lowest index) with the
+            // smallest error replaces the best if it is strictly better -- what the sequential `<` scan ends with
+            if (tid < 32) {
+                double e = DBLMAX;
+                int bp = 0x7fffffff;
+                for (int p2 = tid; p2 < nh; p2 += 32) {
+                    const double ep = err_of(p2);
+                    if (ep < e) { e = ep; bp = p2; }
+                }
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) {
+                    const double eo = __shfl_xor_sync(0xffffffffu, e, d);
+                    const int po = __shfl_xor_sync(0xffffffffu, bp, d);
+                    if (eo < e || (eo == e && po < bp)) { e = eo; bp = po; }
+                }
+                if (e < s.best.error) {  // warp-uniform
+                    __syncwarp();
+                    if (tid < 12) ((double*)&s.best.w2c)[tid] = ((const double*)&s.cand_w2c[bp])[tid];
+                    else if (tid < 24) ((double*)&s.best.c2w)[tid - 12] = ((const double*)&s.cand_c2w[bp])[tid - 12];
+                    else if (tid == 24) s.best.error = e;
+                }
+            }
+            __syncthreads();
+            if (ph == a.iterations) {
+                if (tid == 0 && tr) {
+                    tr->optimized_error = s.best.error;
+                    for (int k = 0; k < 9; ++k) tr->optimized_w2c[k] = s.best.w2c.R[k];
+                    for (int k = 0; k < 3; ++k) tr->optimized_w2c[9 + k] = s.best.w2c.t[k];
+                }
+                tick(1);
+            }
+            continue;
+        }
+        for (int i = tid; i < nh; i += SNT) s.err[i] = err_of(i);
         __syncthreads();
         if (ph == 0) {
             if (tid == 0) {
@@ -483,18 +518,6 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
                 if (tr) tr->first_best_error = s.err[bi];
             }
             tick(0);
-        } else if (ph <= a.iterations) {
-            if (tid == 0) {
-                int bp = -1;
-                double be = s.best.error;
-                for (int p = 0; p < a.particles; ++p)
-                    if (s.err[p] < be) { be = s.err[p]; bp = p; }
-                if (bp >= 0) {
-                    s.best.w2c = s.cand_w2c[bp];
-                    s.best.c2w = s.cand_c2w[bp];
-                    s.best.error = be;
-                }
-            }
         } else {
             if (tr)
                 for (int i = tid; i < ns && i < 81; i += SNT) tr->shift_err[i] = s.err[i];
