@@ -185,6 +185,9 @@ def main():
     if world > 1:
         import torch.distributed as dist
 
+        # the contract is ONE JSON line on stdout: NCCL prints its version banner there when NCCL_DEBUG=VERSION
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
