@@ -153,3 +153,25 @@ def test_localize_full_batch_properties(ctx):
         dz.append(abs(res[i].pos[2] - ps[i][1][2]))
     assert max(ang) < 0.25 and np.median(ang) < 0.06
     assert max(dz) < 0.3 and np.median(dz) < 0.06
+
+
+@pytest.mark.parametrize("dist", [False, True])
+def test_localize_custom_nonplanar_map(dist):
+    """mantis_set_map with a map that leaves the floor plane (z != 0), with and without lens distortion: the
+    non-planar / distorted instantiations of the scoring loop against the oracle on the same map."""
+    import mantis_b200
+
+    white, red, green = (m.copy() for m in po.make_map())
+    rng = np.random.default_rng(7)
+    white[::3, 2] = rng.uniform(-0.04, 0.04, len(white[::3]))
+    green[:, 2] = 0.02
+    K = K_for(640, 480)
+    D = D_UNIT if dist else np.zeros(4)
+    frames = np.stack([po.render_grid(R, t, K, D, 640, 480) for R, t in poses(3, seed=0x4D414E54 + 9)])
+    with mantis_b200.Context(0) as c:
+        c.set_map(white, red, green)
+        res, tr = c.localize(frames, K, D, want_trace=True)
+    for i in range(len(frames)):
+        otr, _ = po.localize(frames[i], K, D, maps=(white, red, green))
+        assert compare(res[i], tr[i], otr, strict=False) or res[i].status != 0
+        assert tr[i].first_best_error == otr.first_best.error  # the scores of the cluster never depend on the RPP stop test
