@@ -175,3 +175,24 @@ def test_localize_custom_nonplanar_map(dist):
         otr, _ = po.localize(frames[i], K, D, maps=(white, red, green))
         assert compare(res[i], tr[i], otr, strict=False) or res[i].status != 0
         assert tr[i].first_best_error == otr.first_best.error  # the scores of the cluster never depend on the RPP stop test
+
+
+def test_localize_odd_size_and_padded_rows(ctx):
+    """Ragged input: a frame size that is no multiple of 4 or 32 (byte-wise gray path, partial last words,
+    partial tiles), once tightly packed and once with padded rows (stride > 3 W, the 2-D copy path)."""
+    import mantis_b200
+
+    W, H = 651, 487
+    K, D = K_for(W, H), np.zeros(4)
+    frames = np.stack([po.render_grid(R, t, K, D, W, H) for R, t in poses(2, seed=0x4D414E54 + 11)])
+    res, tr = ctx.localize(frames, K, D, want_trace=True)
+    stride = 3 * W + 5
+    padded = np.zeros((len(frames), H, stride), np.uint8)
+    padded[:, :, :3 * W] = frames.reshape(len(frames), H, 3 * W)
+    fr = ctx.make_frames([padded[i] for i in range(len(frames))], W, H, K, D, stride=stride)
+    res_p, _ = ctx.localize_frames(fr, mantis_b200.MEM_HOST)
+    assert bytes(res_p) == bytes(res)
+    for i in range(len(frames)):
+        otr, _ = po.localize(frames[i], K, D)
+        assert compare(res[i], tr[i], otr, strict=False) or res[i].status != 0
+        assert (tr[i].n_contours, tr[i].n_quads) == (otr.n_contours, otr.n_quads)
