@@ -196,3 +196,25 @@ def test_localize_odd_size_and_padded_rows(ctx):
         otr, _ = po.localize(frames[i], K, D)
         assert compare(res[i], tr[i], otr, strict=False) or res[i].status != 0
         assert (tr[i].n_contours, tr[i].n_quads) == (otr.n_contours, otr.n_quads)
+
+
+def test_localize_capacity_limits_are_reported(ctx):
+    """Frames beyond the per-frame capacities (1024 contours, 256 quads; the reference has none) must come back
+    as MANTIS_FRAME_OVERFLOW with the flag that says why, never as a pose; a frame of pure noise (143 contours,
+    no 4-gon survives) must match the oracle."""
+    K, D = K_for(640, 480), np.zeros(4)
+    rng = np.random.default_rng(3)
+    noise = rng.integers(0, 256, (480, 640, 3), dtype=np.uint8)
+    fine, coarse = np.zeros((480, 640, 3), np.uint8), np.zeros((480, 640, 3), np.uint8)
+    for y in range(0, 480, 12):
+        for x in range(0, 640, 12):
+            fine[y + 2:y + 10, x + 2:x + 10] = 255      # 2 x 1060 borders + the frame's
+    for y in range(0, 480, 24):
+        for x in range(0, 640, 24):
+            coarse[y + 3:y + 21, x + 3:x + 21] = 255    # 520 squares
+    res, tr = ctx.localize(np.stack([noise, fine, coarse]), K, D, want_trace=True)
+    otr, _ = po.localize(noise, K, D)
+    assert compare(res[0], tr[0], otr)
+    for i in (1, 2):
+        assert res[i].status == 4 and tr[i].flags != 0
+        assert res[i].error == 0 and all(v == 0 for v in res[i].pos[:])
