@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096, help="frames per GPU per step")
     ap.add_argument("--cpu-frames-per-core", type=int, default=4)
-    ap.add_argument("--cpu-reps", type=int, default=16, help="passes over the CPU sample inside its timer")
+    ap.add_argument("--cpu-reps", type=int, default=40, help="passes over the CPU sample inside its timer")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
