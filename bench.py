@@ -82,6 +82,11 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
+    def mark(self):
+        """Call at the start of the timed region: samples before it (the warm-up steps, same load) are only used
+        when nvidia-smi delivered none inside the region (a short region, or eight nvidia-smi processes at once)."""
+        self.first = len(self.rows)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -89,7 +94,12 @@ class ClockSampler:
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        first = getattr(self, "first", 0)
+        window = "timed region"
+        rows = self.rows[first:]
+        if not rows:
+            rows, window = self.rows[-5:], "warm-up steps (no sample arrived inside the timed region)"
+        for r in rows:
             if len(r) < 9:
                 continue
             try:
@@ -101,7 +111,7 @@ class ClockSampler:
                 if r[5 + k].lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 def hbm_peak():
@@ -215,12 +225,13 @@ def main():
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
 
     # ---- device-resident arm ----
+    sampler = ClockSampler(local)
+    sampler.start()  # before the warm-up: nvidia-smi needs a moment to deliver its first line
     for _ in range(args.warmup):
         res, _ = ctx.localize_frames(dframes, mantis_b200.MEM_DEVICE)
     status = np.bincount([r.status for r in res], minlength=5).tolist()
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
+    sampler.mark()
     l0 = ctx.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
