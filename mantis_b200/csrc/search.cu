@@ -212,8 +212,8 @@ __device__ __forceinline__ bool project_bf(const double2* __restrict__ wp, const
     const double iz = fast_rcp3(c[2]);
     const double x = c[0] * iz, y = c[1] * iz;
     const double r2 = fma(x, x, y * y);
-    const bool mid = r2 > KC[1] && r2 < KC[2];
-    ok = ok && r2 < KC[2];  // also drops NaN
+    const bool mid = r2 > KC[1];  // the reference's r > 1e-8; (r2 = 0 gives NaN below, the select still takes 1)
+    ok = ok && r2 < KC[2];        // overflow; also drops NaN
     const double inv_r = fast_rsqrt3(r2), r = r2 * inv_r;
     // fast_atan_pos with an index that is safe for garbage input
     const bool big = r > 1.0;
