@@ -586,8 +586,13 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
             const uint8_t* p = im.bgr + (size_t)y0 * im.stride + 3 * x;
 #pragma unroll
             for (int dy = 0; dy < 10; ++dy, p += im.stride) {
-                const int db = (int)__ldg(p) - 50, dg = (int)__ldg(p + 1) - 255, dr = (int)__ldg(p + 2) - 85;
-                acc += (unsigned)(db * db + dg * dg + dr * dr);
+                // the pixel from the two aligned words that hold it; |c - target| per byte, then one IDP.4A
+                const uintptr_t q = (uintptr_t)p;
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(q & ~(uintptr_t)3);
+                const unsigned sh = ((unsigned)q & 3u) << 3;
+                const uint32_t w0 = __ldg(w), w1 = sh >= 16u ? __ldg(w + 1) : 0u;
+                const uint32_t d = __vabsdiffu4(__funnelshift_r(w0, w1, sh) & 0xffffffu, 0x0055FF32u);  // (B, G, R) = (50, 255, 85)
+                acc = __dp4a(d, d, acc);
             }
         } else {
             for (int dy = 0; dy < 10; ++dy) acc += (unsigned)pixel_err(im, x, y0 + dy, false, 50, 255, 85);
