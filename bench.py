@@ -191,6 +191,16 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: libmantis_cuda has no CPU fallback")
     torch.cuda.set_device(local)
+    if world > 1:
+        # several ranks share the host: keep each one (its pinned staging memory, its copy-issuing thread) on the
+        # CPUs next to its GPU, or the end-to-end arm crosses the socket interconnect
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+        except Exception:  # noqa: BLE001 -- affinity is an optimisation, never a requirement
+            pass
     dist = None
     if world > 1:
         import torch.distributed as dist
