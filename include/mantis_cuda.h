@@ -297,6 +297,17 @@ int mantis_render_grid_batch(mantis_ctx* ctx, const double* poses_w2c, int n, in
                              float noise_sigma, uint32_t seed, uint8_t* d_bgr_out, int stride_bytes,
                              size_t frame_pitch_bytes);
 
+/*
+ * BASELINE.json configs[3]'s frame degradation on the device ("1920x1080 synthetic grid frames with noise/blur"):
+ * separable Gaussian blur (7 taps, sigma in pixels, BORDER_REFLECT_101; sigma 0 = none), then additive
+ * N(0, noise_sigma) per channel (counter-based hash of seed, frame, pixel), rounded and clipped to 8 bits.
+ * Both buffers are DEVICE memory and must not alias.  A frame source, like mantis_render_grid_batch; the
+ * reference has no counterpart (its frames come from a camera).
+ */
+int mantis_degrade_batch(mantis_ctx* ctx, const uint8_t* d_bgr_in, uint8_t* d_bgr_out, int n, int width, int height,
+                         int stride_in, size_t pitch_in, int stride_out, size_t pitch_out, float blur_sigma,
+                         float noise_sigma, uint32_t seed);
+
 #ifdef __cplusplus
 }
 #endif

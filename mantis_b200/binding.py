@@ -181,6 +181,8 @@ def load_library():
     lib.mantis_render_grid_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p,
                                              c.c_void_p, c.c_double, c.c_int, c.c_float, c.c_uint32, c.c_void_p,
                                              c.c_int, c.c_size_t]
+    lib.mantis_degrade_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
+                                         c.c_int, c.c_size_t, c.c_float, c.c_float, c.c_uint32]
     lib.mantis_set_profiling.argtypes = [c.c_void_p, c.c_int]
     lib.mantis_get_stage_ms.argtypes = [c.c_void_p, c.c_void_p]
     _LIB = lib
@@ -428,6 +430,12 @@ class Context:
                                                 float(line_width), int(floor_level), float(noise_sigma), int(seed),
                                                 _ptr(d_out), 3 * w, 3 * w * h)
         self._check(rc, "mantis_render_grid_batch")
+
+    def degrade_device(self, d_in, d_out, n, w, h, blur_sigma=1.5, noise_sigma=8.0, seed=0):
+        """BASELINE configs[3]'s blur + noise on device-resident frames (tightly packed); d_in != d_out."""
+        rc = self._lib.mantis_degrade_batch(self._h, _ptr(d_in), _ptr(d_out), n, w, h, 3 * w, 3 * w * h, 3 * w, 3 * w * h,
+                                            float(blur_sigma), float(noise_sigma), int(seed))
+        self._check(rc, "mantis_degrade_batch")
 
     STAGES = ("h2d", "edge_candidates", "edge_link", "quads", "pose", "search", "d2h")
 

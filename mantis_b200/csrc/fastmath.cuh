@@ -7,6 +7,10 @@
 // Newton steps in fp64 (relative error a few 1e-16, i.e. the same last-bit neighbourhood as the
 // library routines).  search.cu's atan adds a 128-entry table of (theta_i, tan theta_i) and the addition
 // formula, so only a degree-7 odd polynomial on |x| <= 0.0123 remains.
+#ifdef MANTIS_HOST_EMUL  // tools/rpp_emul only (a host build of the pose code for diagnostics); never in the library
+__device__ __forceinline__ double rcp_seed(double x) { return (double)(1.0f / (float)x); }
+__device__ __forceinline__ double rsqrt_seed(double x) { return (double)(float)(1.0 / sqrt(x)); }
+#else
 __device__ __forceinline__ double rcp_seed(double x)  // MUFU.RCP64H: relative error 2^-23
 {
     double y;
@@ -19,6 +23,7 @@ __device__ __forceinline__ double rsqrt_seed(double x)  // MUFU.RSQ64H: relative
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
     return y;
 }
+#endif
 __device__ __forceinline__ double fast_rcp(double z)  // z normal and finite
 {
     double y = rcp_seed(z);

@@ -100,8 +100,9 @@ __global__ void __launch_bounds__(RNT, RUN_CTAS) k_pose_run(PoseArgs a, int roun
     int* fetch = HAS_INIT ? &a.cnt->fetch2[round] : &a.cnt->fetch1[round];
     RunOut* out = HAS_INIT ? a.run2 : a.run1;
     rppf::Lane L;
-    double old_err = 0, new_err = 0;
-    int task = -1, pending = 0, it = 0;
+    rppf::Run S;
+    S.it = 0; S.pending = 0; S.old_err = S.new_err = 0;
+    int task = -1;
     bool exhausted = false;
     for (int trip = 0;; ++trip) {
         if ((trip & 3) == 0) {
@@ -120,13 +121,7 @@ __global__ void __launch_bounds__(RNT, RUN_CTAS) k_pose_run(PoseArgs a, int roun
                         double m[8];
                         model_xy(a.half_spacing, entry & 1, m);
                         rppf::setup(ctx, RNT, a.rays + (size_t)(entry >> 1) * 8, m, L);
-                        it = 0;
-                        if (HAS_INIT) {
-                            old_err = rppf::init_from_R(ctx, RNT, a.candR + (size_t)task * 9, L);
-                            pending = 1;
-                        } else {
-                            pending = 2;  // the run starts from the rays themselves (setup)
-                        }
+                        rppf::run_begin(ctx, RNT, L, S, HAS_INIT ? a.candR + (size_t)task * 9 : nullptr);
                     } else {
                         exhausted = true;
                     }
@@ -134,25 +129,12 @@ __global__ void __launch_bounds__(RNT, RUN_CTAS) k_pose_run(PoseArgs a, int roun
             }
             if (__ballot_sync(0xffffffffu, task >= 0) == 0) break;
         }
-        if (task >= 0) {
-            const double e = rppf::abs_kernel(ctx, RNT, L);
-            bool stop = false;
-            if (pending == 2) {
-                old_err = e;
-                pending = 1;
-            } else {
-                if (pending == 0) old_err = new_err;
-                new_err = e;
-                pending = 0;
-                stop = !(fabs(old_err - new_err) > TOL * fabs(old_err) && new_err > EPSILON) || ++it > 100000;  // |(old - new) / old| > TOL without the division
-            }
-            if (stop) {
-                if (a.dbg && !HAS_INIT) atomicAdd((unsigned long long*)&a.dbg[10 + (it >= 16) + (it >= 64) + (it >= 256) + (it >= 1024) + (it >= 4096)], (unsigned long long)it);
-                RunOut o;
-                rppf::finalize(ctx, RNT, L, o.R, o.t, o.obj_err, o.img_err);
-                out[task] = o;
-                task = -1;
-            }
+        if (task >= 0 && rppf::run_step(ctx, RNT, L, S, TOL, EPSILON)) {
+            if (a.dbg && !HAS_INIT) atomicAdd((unsigned long long*)&a.dbg[10 + (S.it >= 16) + (S.it >= 64) + (S.it >= 256) + (S.it >= 1024) + (S.it >= 4096)], (unsigned long long)S.it);
+            RunOut o;
+            rppf::finalize(ctx, RNT, L, o.R, o.t, o.obj_err, o.img_err);
+            out[task] = o;
+            task = -1;
         }
     }
 }

@@ -71,7 +71,84 @@ __global__ void __launch_bounds__(256) k_render(RenderArgs a)
     o[0] = (uint8_t)b; o[1] = (uint8_t)g; o[2] = (uint8_t)r;
 }
 
+// BASELINE configs[3]'s degradation: Gaussian blur (sigma px, 7x7 taps, BORDER_REFLECT_101) then additive
+// N(0, noise_sigma) per channel from the same counter-based hash, rounded and clipped to u8.
+struct DegradeArgs {
+    const uint8_t* in;
+    uint8_t* out;
+    int W, H, stride_in, stride_out;
+    size_t pitch_in, pitch_out;
+    float taps[7];
+    float noise_sigma;
+    uint32_t seed;
+};
+
+__global__ void __launch_bounds__(256) k_degrade(DegradeArgs a)
+{
+    const int u = blockIdx.x * 64 + (threadIdx.x & 63), v = blockIdx.y * 4 + (threadIdx.x >> 6), f = blockIdx.z;
+    if (u >= a.W || v >= a.H) return;
+    const uint8_t* src = a.in + (size_t)f * a.pitch_in;
+    float acc[3] = {0.f, 0.f, 0.f};
+    for (int dy = -3; dy <= 3; ++dy) {
+        int y = v + dy;
+        y = y < 0 ? -y : (y >= a.H ? 2 * a.H - 2 - y : y);
+        y = min(max(y, 0), a.H - 1);
+        float row[3] = {0.f, 0.f, 0.f};
+        for (int dx = -3; dx <= 3; ++dx) {
+            int x = u + dx;
+            x = x < 0 ? -x : (x >= a.W ? 2 * a.W - 2 - x : x);
+            x = min(max(x, 0), a.W - 1);
+            const uint8_t* p = src + (size_t)y * a.stride_in + 3 * x;
+            const float t = a.taps[dx + 3];
+            row[0] += t * (float)p[0]; row[1] += t * (float)p[1]; row[2] += t * (float)p[2];
+        }
+        const float t = a.taps[dy + 3];
+        acc[0] += t * row[0]; acc[1] += t * row[1]; acc[2] += t * row[2];
+    }
+    const uint32_t idx = ((uint32_t)f * (uint32_t)a.H + (uint32_t)v) * (uint32_t)a.W + (uint32_t)u;
+    uint8_t* o = a.out + (size_t)f * a.pitch_out + (size_t)v * a.stride_out + 3 * u;
+    for (int k = 0; k < 3; ++k) {
+        float val = acc[k];
+        if (a.noise_sigma > 0.f) {
+            uint32_t h1 = hash32(idx * 3u + k + a.seed), h2 = hash32(h1 ^ 0x9e3779b9u);
+            float u1 = ((h1 >> 8) + 1) * (1.0f / 16777216.0f), u2 = (h2 >> 8) * (1.0f / 16777216.0f);
+            val += a.noise_sigma * sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
+        }
+        o[k] = (uint8_t)min(255, max(0, __float2int_rn(val)));
+    }
+}
+
 }  // namespace
+
+extern "C" int mantis_degrade_batch(mantis_ctx* c, const uint8_t* d_bgr_in, uint8_t* d_bgr_out, int n, int width, int height,
+                                    int stride_in, size_t pitch_in, int stride_out, size_t pitch_out, float blur_sigma,
+                                    float noise_sigma, uint32_t seed)
+{
+    if (!c || !d_bgr_in || !d_bgr_out || d_bgr_in == d_bgr_out || n < 0 || width <= 0 || height <= 0 ||
+        stride_in < 3 * width || stride_out < 3 * width || !(blur_sigma >= 0.f) || !(noise_sigma >= 0.f))
+        return MANTIS_ERR_INVALID;
+    if (n == 0) return MANTIS_OK;
+    MCHECK(c, cudaSetDevice(c->device));
+    DegradeArgs a;
+    a.in = d_bgr_in; a.out = d_bgr_out; a.W = width; a.H = height;
+    a.stride_in = stride_in; a.stride_out = stride_out; a.pitch_in = pitch_in; a.pitch_out = pitch_out;
+    double t[7], sum = 0;
+    for (int k = 0; k < 7; ++k) { t[k] = blur_sigma > 0.f ? exp(-(k - 3) * (k - 3) / (2.0 * blur_sigma * blur_sigma)) : (k == 3); sum += t[k]; }
+    for (int k = 0; k < 7; ++k) a.taps[k] = (float)(t[k] / sum);
+    a.noise_sigma = noise_sigma; a.seed = seed;
+    for (int f0 = 0; f0 < n; f0 += 32768) {
+        const int nf = n - f0 < 32768 ? n - f0 : 32768;
+        DegradeArgs b = a;
+        b.in = a.in + (size_t)f0 * pitch_in;
+        b.out = a.out + (size_t)f0 * pitch_out;
+        dim3 grid((width + 63) / 64, (height + 3) / 4, nf);
+        k_degrade<<<grid, 256, 0, c->stream>>>(b);
+        c->launches++;
+        MCHECK(c, cudaGetLastError());
+    }
+    MCHECK(c, cudaStreamSynchronize(c->stream));
+    return MANTIS_OK;
+}
 
 extern "C" int mantis_render_grid_batch(mantis_ctx* c, const double* poses_w2c, int n, int width, int height,
                                         const float* K, const double* D, double line_width, int floor_level,

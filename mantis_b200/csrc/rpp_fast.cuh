@@ -24,9 +24,17 @@
 // A run is a chain of dependent steps and the longest runs (thousands of steps) set the duration of
 // the whole launch, so what matters is the LATENCY of a step: all matrix-vector products above
 // depend only on (a, b) and issue beside the scalar chain (a, b) -> c, after which a', b' are three
-// multiply-adds away.  R, t and the error hang off that chain.  The state of a run is (a, b, r1, r2, t).  The error used by the stopping rule carries the cancellation of that
-// difference (~1e-14 absolute, against errors of 1e-8 and up and a relative tolerance of 1e-5);
-// the error reported at the end is recomputed point by point.
+// multiply-adds away.  R, t and the error hang off that chain.  The state of a run is (a, b, r1, r2, t).
+//
+// The error that feeds the stopping rule (RPP.cpp:171, |(old - new) / old| > 1e-5) is accumulated point
+// by point from (R, t), as the reference does.  The closed quadratic form above would be cheaper, but it
+// carries the cancellation of that difference (~1e-14 absolute against errors down to 1e-8, i.e. 1e-6
+// relative, a tenth of the tolerance): measured on the quads of 1024 rendered frames
+// (tools/rpp_emul/compare.py) it moved the stop by one or more iterations in 30 of 112 790 solves, in
+// 15 of the 1024 frames -- and a run that stops one step apart hands the scoring stage a pose 1e-6
+// away, enough to flip a pixel rounding and send the greedy refinement down another path.  With the
+// point-by-point error the same experiment gives 0 of 112 790.  The extra work (4 points x ~16 fp64
+// operations) is off the dependent chain.
 #pragma once
 #include "fastmath.cuh"
 #include "rpp.cuh"
@@ -39,8 +47,8 @@ constexpr int NPT = 4;
 // Symmetric matrices are stored as xx xy xz yy yz zz.
 // Kxy is general (row-major, 9 words).
 enum {
-    C_VX = 0, C_VY = 4, C_PX = 8, C_PY = 12, C_KXX = 16, C_KXY = 22, C_KYY = 31, C_GX = 37, C_GY = 43, C_G1 = 49, C_TF = 55,
-    C_CXX = 61, C_CXY = 62, C_CYY = 63, C_PBX = 64, C_PBY = 65, CTX_WORDS = 66
+    C_VX = 0, C_VY = 4, C_PX = 8, C_PY = 12, C_KXX = 16, C_KXY = 22, C_KYY = 31, C_GX = 37, C_GY = 43, C_IVV = 49, C_TF = 53,
+    C_PBX = 59, C_PBY = 60, CTX_WORDS = 61
 };
 
 struct Lane {            // registers of one run
@@ -84,7 +92,7 @@ __device__ inline void setup(double* ctx, int stride, const double* ray_xy, cons
     double pbx = 0, pby = 0;
     for (int i = 0; i < NPT; ++i) { pbx += model_xy[2 * i]; pby += model_xy[2 * i + 1]; }
     pbx /= NPT; pby /= NPT;
-    double gxx[6], gxy[6], gyy[6], gx[6], gy[6], g1[6], cxx = 0, cxy = 0, cyy = 0;
+    double gxx[6], gxy[6], gyy[6], gx[6], gy[6], g1[6];
     for (int k = 0; k < 6; ++k) gxx[k] = gxy[k] = gyy[k] = gx[k] = gy[k] = g1[k] = 0;
     for (int k = 0; k < 3; ++k) L.a[k] = L.b[k] = L.r1[k] = L.r2[k] = L.t[k] = 0;
     for (int i = 0; i < NPT; ++i) {
@@ -95,6 +103,7 @@ __device__ inline void setup(double* ctx, int stride, const double* ray_xy, cons
         RPPF_C(C_VY + i) = v[1];
         RPPF_C(C_PX + i) = px;
         RPPF_C(C_PY + i) = py;
+        RPPF_C(C_IVV + i) = 1.0 / vv;
         const double f[6] = {(v[0] * v[0]) / vv, (v[0] * v[1]) / vv, (v[0] * v[2]) / vv, (v[1] * v[1]) / vv, (v[1] * v[2]) / vv, (v[2] * v[2]) / vv};
         for (int k = 0; k < 6; ++k) {
             g1[k] += f[k];
@@ -104,7 +113,6 @@ __device__ inline void setup(double* ctx, int stride, const double* ray_xy, cons
             gxy[k] += px * py * f[k];
             gyy[k] += py * py * f[k];
         }
-        cxx += px * px; cxy += px * py; cyy += py * py;
         for (int k = 0; k < 3; ++k) { L.a[k] += px * v[k]; L.b[k] += py * v[k]; }  // F_i v_i = v_i
     }
     L.rays = true;
@@ -134,9 +142,8 @@ __device__ inline void setup(double* ctx, int stride, const double* ray_xy, cons
         }
     for (int k = 0; k < 6; ++k) {
         RPPF_C(C_TF + k) = tF.m[upper[k]] / NPT;
-        RPPF_C(C_GX + k) = gx[k]; RPPF_C(C_GY + k) = gy[k]; RPPF_C(C_G1 + k) = g1[k];
+        RPPF_C(C_GX + k) = gx[k]; RPPF_C(C_GY + k) = gy[k];
     }
-    RPPF_C(C_CXX) = cxx; RPPF_C(C_CXY) = cxy; RPPF_C(C_CYY) = cyy;
     RPPF_C(C_PBX) = pbx;
     RPPF_C(C_PBY) = pby;
 }
@@ -149,35 +156,25 @@ __device__ __forceinline__ void point(const double* ctx, int stride, const Lane&
     for (int k = 0; k < 3; ++k) q[k] = (L.r1[k] * px + L.r2[k] * py) + L.t[k];
 }
 
-// sum |Q_i - F_i Q_i|^2 point by point, as the reference accumulates it
-__device__ inline double point_error(const double* ctx, int stride, const Lane& L)
+// sum |Q_i - F_i Q_i|^2 point by point for Q_i = R P_i + t, as the reference accumulates it
+// (F_i Q_i = v_i (v_i.Q_i) / (v_i.v_i))
+__device__ __forceinline__ double point_error_rt(const double* ctx, int stride, const double* r1, const double* r2, const double* t)
 {
     double err2 = 0;
     for (int i = 0; i < NPT; ++i) {
-        double q[3];
-        point(ctx, stride, L, i, q);
-        const double vx = RPPF_C(C_VX + i), vy = RPPF_C(C_VY + i);
-        const double w = (vx * q[0] + vy * q[1] + q[2]) / (vx * vx + vy * vy + 1.0);
-        const double e0 = q[0] - vx * w, e1 = q[1] - vy * w, e2 = q[2] - w;
-        err2 += e0 * e0 + e1 * e1 + e2 * e2;
+        const double px = RPPF_C(C_PX + i), py = RPPF_C(C_PY + i), vx = RPPF_C(C_VX + i), vy = RPPF_C(C_VY + i);
+        const double q0 = fma(r2[0], py, fma(r1[0], px, t[0])), q1 = fma(r2[1], py, fma(r1[1], px, t[1])),
+                     q2 = fma(r2[2], py, fma(r1[2], px, t[2]));
+        const double w = fma(vy, q1, fma(vx, q0, q2)) * RPPF_C(C_IVV + i);
+        const double e0 = fma(-vx, w, q0), e1 = fma(-vy, w, q1), e2 = q2 - w;
+        err2 = fma(e2, e2, fma(e1, e1, fma(e0, e0, err2)));
     }
     return err2;
 }
-
-// sum |Q_i|^2 - sum Q_i.F_i Q_i for Q_i = R P_i + t, given a = sum px_i F_i Q_i, b = sum py_i F_i Q_i and
-// gs = Gx r1 + Gy r2
-__device__ __forceinline__ double quad_error(const double* ctx, int stride, const double* r1, const double* r2, const double* t,
-                                             const double* a, const double* b, const double* gs)
+__device__ inline double point_error(const double* ctx, int stride, const Lane& L)
 {
-    double g[3];
-    symv(ctx, stride, C_G1, t, g);
-    double qfq = 0, r11 = 0, r12 = 0, r22 = 0, tt = 0;
-    for (int k = 0; k < 3; ++k) {
-        qfq = fma(r1[k], a[k], fma(r2[k], b[k], fma(t[k], gs[k] + g[k], qfq)));
-        r11 = fma(r1[k], r1[k], r11); r12 = fma(r1[k], r2[k], r12); r22 = fma(r2[k], r2[k], r22); tt = fma(t[k], t[k], tt);
-    }
-    const double qq = fma(RPPF_C(C_CXX), r11, fma(2.0 * RPPF_C(C_CXY), r12, fma(RPPF_C(C_CYY), r22, NPT * tt)));
-    return qq - qfq;
+    if (!L.rays) return point_error_rt(ctx, stride, L.r1, L.r2, L.t);
+    return 0;  // the rays lie on their own lines of sight
 }
 
 // With (r1, r2) set and t = tF (Gx r1 + Gy r2): t, a, b of the new points and their error.
@@ -192,7 +189,7 @@ __device__ inline double refresh(const double* ctx, int stride, Lane& L)
     genv2(ctx, stride, C_KXY, L.r2, L.r1, ta, tb);
     for (int k = 0; k < 3; ++k) { L.a[k] += ta[k]; L.b[k] += tb[k]; }
     L.rays = false;
-    return quad_error(ctx, stride, L.r1, L.r2, L.t, L.a, L.b, gs);
+    return point_error_rt(ctx, stride, L.r1, L.r2, L.t);
 }
 
 // The general step through the 3x3 SVD (rare): rebuilds the reference-shaped context.
@@ -268,7 +265,7 @@ __device__ __forceinline__ double abs_kernel(const double* ctx, int stride, Lane
     }
     symv(ctx, stride, C_TF, gs, t);   // t = tF * sum F_i (R P_i)
     if (t[2] < 0) return abs_kernel_general(ctx, stride, L);
-    const double err2 = quad_error(ctx, stride, r1, r2, t, an, bn, gs);
+    const double err2 = point_error_rt(ctx, stride, r1, r2, t);
     for (int k = 0; k < 3; ++k) { L.r1[k] = r1[k]; L.r2[k] = r2[k]; L.t[k] = t[k]; L.a[k] = an[k]; L.b[k] = bn[k]; }
     L.rays = false;
     return err2;
@@ -300,6 +297,41 @@ __device__ inline void finalize(const double* ctx, int stride, const Lane& L, do
     img_err = sqrt(ie / NPT);
     const double pbx = RPPF_C(C_PBX), pby = RPPF_C(C_PBY);
     for (int k = 0; k < 3; ++k) t3[k] = L.t[k] - (L.r1[k] * pbx + L.r2[k] * pby);
+}
+
+// ---- one ObjPose run as a resumable state machine (RPP.cpp:66-208) --------------------------------
+// run_begin() after setup(); then run_step() until it returns true; then finalize().
+struct Run {
+    double old_err, new_err;
+    int it;        // stop tests made so far
+    int pending;   // 2: the next step gives old_err (run without initial R), 1: next step gives the first new_err
+};
+__device__ __forceinline__ void run_begin(const double* ctx, int stride, Lane& L, Run& S, const double* initR9)
+{
+    S.it = 0;
+    S.new_err = 0;
+    if (initR9) {
+        S.old_err = init_from_R(ctx, stride, initR9, L);
+        S.pending = 1;
+    } else {
+        S.old_err = 0;
+        S.pending = 2;  // the run starts from the rays themselves (setup)
+    }
+}
+// One AbsKernel step and the reference's stopping rule.  Returns true when the run is over.
+__device__ __forceinline__ bool run_step(const double* ctx, int stride, Lane& L, Run& S, double TOL, double EPSILON)
+{
+    const double e = abs_kernel(ctx, stride, L);
+    if (S.pending == 2) {
+        S.old_err = e;
+        S.pending = 1;
+        return false;
+    }
+    if (S.pending == 0) S.old_err = S.new_err;
+    S.new_err = e;
+    S.pending = 0;
+    // |(old - new) / old| > TOL without the division
+    return !(fabs(S.old_err - S.new_err) > TOL * fabs(S.old_err) && S.new_err > EPSILON) || ++S.it > 100000;
 }
 
 #undef RPPF_C
