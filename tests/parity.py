@@ -60,8 +60,13 @@ def _oracle_frame(i):
 
 
 def rot_angle(q1, q2):
-    d = abs(float(np.dot(q1, q2)))
-    return 2 * np.arccos(min(1.0, d))
+    """Angle of the rotation between two unit quaternions (x y z w), accurate near 0: 2 atan2(|v|, |w|) of q1^-1 q2."""
+    x1, y1, z1, w1 = q1
+    x2, y2, z2, w2 = q2
+    w = w1 * w2 + x1 * x2 + y1 * y2 + z1 * z2
+    v = np.array([w1 * x2 - x1 * w2 - y1 * z2 + z1 * y2, w1 * y2 + x1 * z2 - y1 * w2 - z1 * x2,
+                  w1 * z2 - x1 * y2 + y1 * x2 - z1 * w2])
+    return 2 * float(np.arctan2(np.linalg.norm(v), abs(w)))
 
 
 def compare_frame(res, tr, fq, o):
