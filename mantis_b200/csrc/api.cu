@@ -1,6 +1,7 @@
 // api.cu -- C ABI entry points (include/mantis_cuda.h): context life cycle and the
 // image-stage batch call.  No CPU fallback: without a CUDA device creation fails.
 #include <new>
+#include <stdlib.h>
 #include "ctx.h"
 
 int ctx_init_tables(mantis_ctx* c);
@@ -182,10 +183,15 @@ int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int hei
     for (int f0 = 0; f0 < n; f0 += 32768) {
         int nf = (n - f0 < 32768) ? (n - f0) : 32768;
         size_t poff = (size_t)f0 * height * WW, moff = (size_t)f0 * height * width;
-        if ((rc = launch_edge_candidates(c, d_in + (size_t)f0 * frame_pitch_bytes, nf, width, height, stride_bytes,
-                                         frame_pitch_bytes, low, high, (uint32_t*)c->weak.p + poff,
-                                         (uint32_t*)c->strong.p + poff)))
-            return rc;
+        const uint8_t* d_f0 = d_in + (size_t)f0 * frame_pitch_bytes;
+        static const bool force_tiled = getenv("MANTIS_K1_TILED") != nullptr;   // tuning aid: the tiled kernel for every shape
+        if (!force_tiled && edge_march_supported(d_f0, width, height, stride_bytes, frame_pitch_bytes))
+            rc = launch_edge_march(c, d_f0, nf, width, height, stride_bytes, frame_pitch_bytes, low, high,
+                                   (uint32_t*)c->weak.p + poff, (uint32_t*)c->strong.p + poff);
+        else
+            rc = launch_edge_candidates(c, d_f0, nf, width, height, stride_bytes, frame_pitch_bytes, low, high,
+                                        (uint32_t*)c->weak.p + poff, (uint32_t*)c->strong.p + poff);
+        if (rc) return rc;
         prof_mark(c, 2);
         EdgeOutputs eo;
         eo.canny_bits = out.canny_bits ? out.canny_bits + poff : nullptr;

@@ -104,6 +104,10 @@ inline int ctx_reserve_pinned(mantis_ctx* c, void** p, size_t* cap, size_t bytes
 // Candidate kernel: BGR -> gray -> blur -> Sobel -> NMS -> weak / strong bit planes.
 int launch_edge_candidates(mantis_ctx* c, const uint8_t* d_bgr, int n, int w, int h, int stride,
                            size_t frame_pitch, int low, int high, uint32_t* d_weak, uint32_t* d_strong);
+// The same stage in marching form (edge_march.cu) for 16-byte aligned rows and widths that are multiples of 16.
+bool edge_march_supported(const uint8_t* d_bgr, int w, int h, int stride, size_t frame_pitch);
+int launch_edge_march(mantis_ctx* c, const uint8_t* d_bgr, int n, int w, int h, int stride, size_t frame_pitch, int low,
+                      int high, uint32_t* d_weak, uint32_t* d_strong);
 // Per-frame on-chip kernel: hysteresis closure, dilate x2 + erode x1, edge mask; every output optional.
 struct EdgeOutputs {
     uint32_t* canny_bits = nullptr;
