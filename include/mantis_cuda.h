@@ -308,6 +308,28 @@ int mantis_degrade_batch(mantis_ctx* ctx, const uint8_t* d_bgr_in, uint8_t* d_bg
                          int stride_in, size_t pitch_in, int stride_out, size_t pitch_out, float blur_sigma,
                          float noise_sigma, uint32_t seed);
 
+/*
+ * The image stage of mantis_edges_batch() for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  This entry point has NO counterpart in the
+ * reference.  Same kernels, same results as
+ * mantis_edges_batch(..., MANTIS_MEM_DEVICE), but the intermediate weak / strong candidate bit planes live in
+ * a fixed file-scope __device__ array instead of context scratch, so the call performs no cudaMalloc /
+ * cudaFree and calls no allocating library routine.
+ *   - d_bgr, d_canny_out, d_morph_out are DEVICE pointers on the context's device (an output may be NULL,
+ *     not both); layouts as in mantis_edges_batch.
+ *   - limit: 2 * round_up_256(n * height * ceil(width / 32) * 4) <= MANTIS_NOALLOC_SCRATCH_BYTES (8 MiB), i.e.
+ *     up to 109 frames of 640x480, 36 of 1280x720, 16 of 1920x1080 per call.  A larger batch is rejected
+ *     with MANTIS_ERR_INVALID and a message in mantis_last_error(); split it, or use mantis_edges_batch.
+ *   - every GPU that loads the library holds the 8 MiB array until the process exits.
+ *   - all calls on one device SHARE the array, and it keeps the previous call's contents: the part a call
+ *     uses is cleared on the context's stream first.  Two calls that overlap on the GPU (two contexts or
+ *     streams on one device) race on it -- serialise them.
+ * Synchronous with respect to the host, like the other entry points.
+ */
+#define MANTIS_NOALLOC_SCRATCH_BYTES ((size_t)8 << 20)
+int mantis_edges_noalloc(mantis_ctx* ctx, const uint8_t* d_bgr, int n, int width, int height, int stride_bytes,
+                         size_t frame_pitch_bytes, uint8_t* d_canny_out, uint8_t* d_morph_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -120,6 +120,7 @@ class PnpResult(ctypes.Structure):
 
 
 PNP_BOTH_PLANAR = 1
+NOALLOC_SCRATCH_BYTES = 8 << 20  # MANTIS_NOALLOC_SCRATCH_BYTES
 
 
 def library_path():
@@ -183,6 +184,8 @@ def load_library():
                                              c.c_int, c.c_size_t]
     lib.mantis_degrade_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
                                          c.c_int, c.c_size_t, c.c_float, c.c_float, c.c_uint32]
+    lib.mantis_edges_noalloc.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t, c.c_void_p,
+                                         c.c_void_p]
     lib.mantis_set_profiling.argtypes = [c.c_void_p, c.c_int]
     lib.mantis_get_stage_ms.argtypes = [c.c_void_p, c.c_void_p]
     _LIB = lib
@@ -268,6 +271,14 @@ class Context:
         rc = self._lib.mantis_edges_batch(self._h, _ptr(d_bgr), n, w, h, stride, pitch, _ptr(d_canny), _ptr(d_morph),
                                           MEM_DEVICE)
         self._check(rc, "mantis_edges_batch")
+
+    def edges_noalloc(self, d_bgr, n, w, h, d_canny=None, d_morph=None, stride=None, pitch=None):
+        """mantis_edges_noalloc: the device-resident image stage with its scratch in a fixed __device__ array
+        (no cudaMalloc inside the call; at most NOALLOC_SCRATCH_BYTES of bit planes per call)."""
+        stride = 3 * w if stride is None else stride
+        pitch = stride * h if pitch is None else pitch
+        rc = self._lib.mantis_edges_noalloc(self._h, _ptr(d_bgr), n, w, h, stride, pitch, _ptr(d_canny), _ptr(d_morph))
+        self._check(rc, "mantis_edges_noalloc")
 
     # -- cleanImageByEdge mask, HypothesisEvaluation.h:319-386 --
     def edge_mask(self, bgr):
