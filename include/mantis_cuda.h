@@ -16,8 +16,10 @@
  *   - every function returns MANTIS_OK (0) or a negative mantis_status; nothing
  *     throws or exits across the ABI (the reference exit(1)s inside RPP.cpp:452).
  *   - `mem` says where the caller's image / result buffers live: MANTIS_MEM_HOST
- *     (the library stages them through pinned memory and copies on its stream) or
- *     MANTIS_MEM_DEVICE (pointers are device pointers on the context's device).
+ *     (the library copies straight from / to the caller's buffers on its streams --
+ *     pin them with cudaHostAlloc / cudaHostRegister if the copy is to overlap the
+ *     kernels; pageable memory works, synchronously) or MANTIS_MEM_DEVICE (pointers
+ *     are device pointers on the context's device).
  *   - a context is bound to one device and one stream; one context per host
  *     thread.  No allocation happens on the hot calls once the context has seen
  *     the largest batch / frame size (scratch grows monotonically).
@@ -208,7 +210,7 @@ int mantis_pnp_batch(mantis_ctx* ctx, const float* obj_xyz, const float* img_xy,
 typedef struct mantis_frame {     /* one sensor_msgs/Image + CameraInfo of mantisService.srv:1-2 */
     const uint8_t* bgr;           /* 8-bit BGR, HWC (host or device, see `mem`) */
     int32_t width, height, stride_bytes;
-    float K[9];                   /* CameraInfo.K as the CV_32F 3x3 of get3x3FromVector, QuadDetection.h:189-201 */
+    float K[9];                   /* CameraInfo.K as the CV_32F 3x3 of get3x3FromVector, QuadDetection.h:189-201; K[1] (skew) must be 0 */
     double D[4];                  /* CameraInfo.D, fisheye coefficients (src/mantis3.cpp:74) */
     double cam_to_base[7];        /* optional camera->base_link transform (x y z qx qy qz qw); identity if qw==0 */
     uint64_t stamp_ns;

@@ -1,6 +1,7 @@
 // api.cu -- C ABI entry points (include/mantis_cuda.h): context life cycle and the
 // image-stage batch call.  No CPU fallback: without a CUDA device creation fails.
 #include <new>
+#include <cmath>
 #include <stdlib.h>
 #include "ctx.h"
 
@@ -42,10 +43,27 @@ const char* mantis_strerror(int status)
     }
 }
 
+// Limits the kernels are built for (search.cu: 96 particles / 96 cell shifts per frame), checked once here
+// instead of on the first localize call.
+static bool config_valid(const mantis_config& g)
+{
+    auto pos = [](double v) { return std::isfinite(v) && v > 0; };
+    if (g.canny_hysteresis < 0 || g.canny_hysteresis > 680 || g.polygon_epsilon < 0) return false;   // 3T must stay below the fp16 magnitude range (2040)
+    if (g.particles < 0 || g.particles > 96 || g.iterations < 0 || g.iterations > 4096) return false;
+    if ((long long)g.particles * g.iterations > 100000) return false;
+    if (g.grid_size < 1 || (long long)g.grid_size * g.grid_size > 96) return false;
+    if (!pos(g.grid_spacing) || !pos(g.projection_bias) || !pos(g.color_projection_bias)) return false;
+    if (!pos(g.quad_stretch_factor) || !std::isfinite(g.search_radius_multiplier) || g.search_radius_multiplier < 0) return false;
+    if (!std::isfinite(g.max_quad_error) || !std::isfinite(g.max_angle_difference) || g.max_angle_difference < 0) return false;
+    if (!std::isfinite(g.rot_sigma) || g.rot_sigma < 0 || !std::isfinite(g.trans_sigma) || g.trans_sigma < 0) return false;
+    return true;
+}
+
 int mantis_create(const mantis_config* cfg, int device, mantis_ctx** out)
 {
     if (!out) return MANTIS_ERR_INVALID;
     *out = nullptr;
+    if (cfg && !config_valid(*cfg)) return MANTIS_ERR_INVALID;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MANTIS_ERR_NO_DEVICE;
     if (device < 0 || device >= ndev) return MANTIS_ERR_INVALID;
@@ -82,8 +100,6 @@ int mantis_destroy(mantis_ctx* c)
                       &c->hough_trig, &c->hough_count, &c->hough_peaks, &c->hough_lines, &c->d_atan, &c->search_ticket, &c->pnp_stage, &c->leg_a, &c->leg_b, &c->leg_c};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
-    if (c->pin_in) cudaFreeHost(c->pin_in);
-    if (c->pin_out) cudaFreeHost(c->pin_out);
     for (int i = 0; i <= MANTIS_N_STAGES; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int i = 0; i < 2; ++i) {

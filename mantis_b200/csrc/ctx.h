@@ -54,8 +54,6 @@ struct mantis_ctx {
     DevBuf stage_in, stage_in2, stage_out0, stage_out1;  // device staging for MANTIS_MEM_HOST callers
     cudaStream_t copy_stream = nullptr;       // H2D of the next chunk while the current one computes
     cudaEvent_t ev_copied[2] = {}, ev_free[2] = {};
-    void* pin_in = nullptr;  size_t pin_in_cap = 0;   // pinned host staging
-    void* pin_out = nullptr; size_t pin_out_cap = 0;
 };
 
 #define MCHECK(ctx, call)                                                                  \

@@ -10,9 +10,9 @@
 // Shape.  A warp owns a 256-px column strip (lane = 8 px = 24 bytes of BGR) and walks down a band of rows;
 // lanes 1..30 produce output (240 px), lanes 0 and 31 only feed their neighbours.  Only the raw rows
 // touch shared memory; every intermediate lives in registers:
-//   rows in    one cp.async.bulk (TMA, 1-D) per row into a 4-slot ring per warp, completion on an mbarrier;
-//              lanes read their 24 bytes with three conflict-free LDS.64.  A warp keeps up to 4 rows
-//              (3 KB) in flight, so 20 resident warps cover HBM latency without a register prefetch.
+//   rows in    one cp.async.bulk (TMA, 1-D) per row into a 3-slot ring per warp, completion on an mbarrier;
+//              lanes read their 24 bytes with three conflict-free LDS.64.  A warp keeps up to 3 rows
+//              (2.3 KB) in flight, so 16 resident warps cover HBM latency without a register prefetch.
 //   gray       two IDP.2A per pixel: the 16-bit operand holds 2 x (3735, 19235, 9798), the byte operand is
 //              the raw BGR word, so no byte alignment / extraction is needed; the value lands in byte 2.
 //              PRMT packs two pixels into a 16x2 pair.
@@ -43,7 +43,7 @@ namespace {
 constexpr int MW = 4;          // warps per CTA (independent; the CTA is a container)
 constexpr int STRIP = 256;     // px per warp, halo lanes included
 constexpr int VALID = 240;     // output px per warp
-constexpr int NSLOT = 4;       // rows in flight per warp
+constexpr int NSLOT = 3;       // rows in flight per warp; slot = ring sequence number % 3 = the unroll phase of the march
 constexpr int SLOT_BYTES = 800;
 
 struct __align__(16) WarpSmem {
@@ -97,6 +97,15 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t pari
                      : "r"(smem_u32(bar)), "r"(parity)
                      : "memory");
     } while (!ok);
+}
+
+// One lane of a converged warp (elect.sync): the copy engine is driven by a single thread, and with an elected
+// lane ptxas emits the R2UR + UBLKCP sequence once instead of a broadcast loop over the active lanes.
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+    return pred != 0;
 }
 
 __device__ __forceinline__ int reflect101(int i, int n)
@@ -268,12 +277,13 @@ __device__ __forceinline__ void nms_row(const uint32_t* Mu, const uint32_t* Su, 
 }
 
 // Bulk copy number q of a warp's march: gray row ybs - 1 + q (reflected into the image) into slot q % NSLOT.
-// Rows nobody will wait for are never requested (a CTA must not exit with copies in flight).
+// Rows nobody will wait for are never requested (a CTA must not exit with copies in flight).  Prologue only;
+// the steps advance a running row pointer instead (march_step).
 __device__ __forceinline__ void ring_issue(const MarchArgs& a, const Task& T, WarpSmem& s, int q, int n_steps)
 {
     const int step = q - 2;
     if (q >= 2 && (step >= n_steps || T.ybs + step >= a.H)) return;
-    const int slot = q & (NSLOT - 1);
+    const int slot = q % NSLOT;
     mbar_expect_tx(&s.full[slot], (uint32_t)T.nbytes);
     bulk_g2s(s.rows[slot], T.img + (size_t)reflect101(T.ybs - 1 + q, a.H) * a.stride + T.a0, (uint32_t)T.nbytes, &s.full[slot]);
 }
@@ -281,17 +291,25 @@ __device__ __forceinline__ void ring_issue(const MarchArgs& a, const Task& T, Wa
 // One step of the march: blur row yb (if it exists) enters the windows, the Sobel runs at yc = yb - 1, the NMS at
 // yn = yb - 2.  PH = step index mod 3 names the window slots, so that nothing is moved between registers.
 template <int PH, bool BORDER>
-__device__ __forceinline__ void march_step(const MarchArgs& a, const Task& T, WarpSmem& s, Win& w, int step, int n_steps, int lane)
+__device__ __forceinline__ void march_step(const MarchArgs& a, const Task& T, WarpSmem& s, Win& w, int step, int n_steps, int lane,
+                                           uint32_t ph, const uint8_t* next_row)
 {
     constexpr int SA = PH % 3, SB = (PH + 1) % 3, SC = (PH + 2) % 3;   // oldest, middle, newest
     const int H = a.H, yb = T.ybs + step;
     if (yb < H) {
-        // ring sequence number q: gray row ybs - 1 + q (q = 0, 1 are the prologue's rows, q = step + 2 this step's)
-        const int q = step + 2, slot = q & (NSLOT - 1);
-        mbar_wait(&s.full[slot], (uint32_t)(q / NSLOT) & 1u);
-        gray_pairs(s.rows[slot], T.lane_off, w.G[SC]);
+        // ring sequence number q = step + 2 (q = 0, 1 are the prologue's rows): slot q % 3 = SC, phase parity (q / 3) & 1
+        mbar_wait(&s.full[SC], ph ^ (PH > 0 ? 1u : 0u));
+        gray_pairs(s.rows[SC], T.lane_off, w.G[SC]);
         __syncwarp();   // every lane has its bytes: the slot may be refilled
-        if (lane == 0) ring_issue(a, T, s, q + NSLOT, n_steps);
+        // ... with gray row yb + 4, the one step + 3 consumes -- if that step exists and has a blur row (yb + 3 < H);
+        // yb + 4 == H is the reflected row H - 2
+        if (step + 3 < n_steps && yb + 3 < H) {
+            if (elect_one()) {
+                const uint8_t* src = next_row - (yb + 4 == H ? 2 * (size_t)a.stride : 0);
+                mbar_expect_tx(&s.full[SC], (uint32_t)T.nbytes);
+                bulk_g2s(s.rows[SC], src, (uint32_t)T.nbytes, &s.full[SC]);
+            }
+        }
         blur_row(w.G[SA], w.G[SB], w.G[SC], T, w.B[SC], w.HD[SC]);
     }
     // rows of this step: yc = yb - 1 gets its Sobel (slot SB), yn = yb - 2 its NMS (slot SA; row yn - 1 sits in SC)
@@ -335,7 +353,7 @@ __device__ __forceinline__ void march_step(const MarchArgs& a, const Task& T, Wa
     }
 }
 
-__global__ void __launch_bounds__(MW * 32) k_edge_march(MarchArgs a)
+__global__ void __launch_bounds__(MW * 32, 4) k_edge_march(MarchArgs a)
 {
     __shared__ WarpSmem sm[MW];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -379,6 +397,7 @@ __global__ void __launch_bounds__(MW * 32) k_edge_march(MarchArgs a)
     __syncwarp();
     if (lane == 0)
         for (int q = NSLOT; q < NSLOT + 2; ++q) ring_issue(a, T, s, q, n_steps);
+    __syncwarp();
 #pragma unroll
     for (int j = 0; j < 6; ++j) w.B[0][j] = w.B[1][j] = w.B[2][j] = 0u;
 #pragma unroll
@@ -392,17 +411,21 @@ __global__ void __launch_bounds__(MW * 32) k_edge_march(MarchArgs a)
     for (int j = 0; j < 5; ++j) w.S[0][j] = w.S[1][j] = w.S[2][j] = 0u;
     // Steps whose Sobel centre is row 0 or row H - 1 take the variant with the border copies; every other group
     // of three runs without them.  (Sobel centre of step k is ybs + k - 1.)
-    for (int step = 0; step < n_steps; step += 3) {
+    // next_row: address of gray row yb + 4 for the step at hand (the row its refill asks for)
+    const uint8_t* next_row = T.img + (size_t)(T.ybs + 4) * a.stride + T.a0;
+    const size_t s1 = (size_t)a.stride;
+    uint32_t ph = 0u;
+    for (int step = 0; step < n_steps; step += 3, ph ^= 1u, next_row += 3 * s1) {
         const int yc0 = T.ybs + step - 1;
         const bool edge = yc0 <= 0 || yc0 + 2 >= a.H - 1;
         if (edge) {
-            march_step<0, true>(a, T, s, w, step, n_steps, lane);
-            if (step + 1 < n_steps) march_step<1, true>(a, T, s, w, step + 1, n_steps, lane);
-            if (step + 2 < n_steps) march_step<2, true>(a, T, s, w, step + 2, n_steps, lane);
+            march_step<0, true>(a, T, s, w, step, n_steps, lane, ph, next_row);
+            if (step + 1 < n_steps) march_step<1, true>(a, T, s, w, step + 1, n_steps, lane, ph, next_row + s1);
+            if (step + 2 < n_steps) march_step<2, true>(a, T, s, w, step + 2, n_steps, lane, ph, next_row + 2 * s1);
         } else {
-            march_step<0, false>(a, T, s, w, step, n_steps, lane);
-            if (step + 1 < n_steps) march_step<1, false>(a, T, s, w, step + 1, n_steps, lane);
-            if (step + 2 < n_steps) march_step<2, false>(a, T, s, w, step + 2, n_steps, lane);
+            march_step<0, false>(a, T, s, w, step, n_steps, lane, ph, next_row);
+            if (step + 1 < n_steps) march_step<1, false>(a, T, s, w, step + 1, n_steps, lane, ph, next_row + s1);
+            if (step + 2 < n_steps) march_step<2, false>(a, T, s, w, step + 2, n_steps, lane, ph, next_row + 2 * s1);
         }
     }
 }

@@ -116,6 +116,13 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     for (int i = 0; i < n; ++i)
         if (!frames[i].bgr || frames[i].width != W || frames[i].height != H || frames[i].stride_bytes != stride0)
             return MANTIS_ERR_INVALID;
+    // the camera model has no skew term (cv::fisheye applies alpha = K(0,1) / fx; the reference's cameras have 0):
+    // refuse it instead of silently ignoring it
+    for (int i = 0; i < n; ++i)
+        if (frames[i].K[1] != 0.0f || !(frames[i].K[0] > 0.0f) || !(frames[i].K[4] > 0.0f)) {
+            snprintf(c->err, sizeof(c->err), "frame %d: K must be upper triangular without skew (K[1] == 0) with positive focal lengths", i);
+            return MANTIS_ERR_INVALID;
+        }
     size_t dev_pitch = (size_t)stride0 * H;
     if (mem == MANTIS_MEM_DEVICE && n > 1) {
         dev_pitch = (size_t)(frames[1].bgr - frames[0].bgr);
@@ -223,9 +230,11 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         MCHECK(c, cudaEventRecord(c->ev_copied[buf], c->copy_stream));
         return MANTIS_OK;
     };
-    if (host && (rc = issue_copy(0))) return rc;
-
     std::vector<pm::Camera> cams((size_t)nc_max);
+    // The chunk loop as one unit: whatever makes it stop early, no copy may still be reading the caller's frames
+    // (or writing the caller's results) once this call has returned.
+    auto run_chunks = [&]() -> int {
+    if (host && (rc = issue_copy(0))) return rc;
     for (int k = 0; k < n_chunks; ++k) {
         const int f0 = start[k], nc = start[k + 1] - f0;
         const uint8_t* d_in;
@@ -280,4 +289,11 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         prof_collect(c, 0, MANTIS_N_STAGES);
     }
     return MANTIS_OK;
+    };
+    rc = run_chunks();
+    if (rc != MANTIS_OK) {  // drain both streams; the first error text is the one worth keeping
+        if (host && c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+        cudaStreamSynchronize(c->stream);
+    }
+    return rc;
 }

@@ -521,12 +521,18 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
         } else {
             if (tr)
                 for (int i = tid; i < ns && i < 81; i += SNT) tr->shift_err[i] = s.err[i];
-            // (11) best 20: position in a stable descending sort; keep the last 20
+            // (11) best 20: position in a stable descending sort; keep the last 20.  With 20 shifts or fewer
+            // (grid_size <= 4) getBestNHypotheses returns the list as it is (HypothesisEvaluation.h:492), so
+            // hyps.back() is the LAST shift, not the best one.
             if (tid < ns) {
-                int pos = 0;
-                const double e = s.err[tid];
-                for (int j = 0; j < ns; ++j) pos += (s.err[j] > e) || (s.err[j] == e && j < tid);
-                if (pos >= ns - keep) s.top20[pos - (ns - keep)] = (short)tid;
+                if (ns <= 20) {
+                    s.top20[tid] = (short)tid;
+                } else {
+                    int pos = 0;
+                    const double e = s.err[tid];
+                    for (int j = 0; j < ns; ++j) pos += (s.err[j] > e) || (s.err[j] == e && j < tid);
+                    if (pos >= ns - keep) s.top20[pos - (ns - keep)] = (short)tid;
+                }
             }
         }
         __syncthreads();

@@ -398,19 +398,22 @@ void mo_clean_mask(const uint8_t* canny, int w, int h, uint8_t* mask)
 /* ------------------------------------------------------------------ scoring */
 static int cv_round(double v) { return (int)lrint(v); }
 
-/* img.at<Vec3b>(Point) with the reference's unchecked linear addressing */
+/* img.at<Vec3b>(Point) with the reference's unchecked linear addressing.  The image the reference indexes is
+ * the clone() of the message's image (src/mantis3.cpp:71) or the copyTo() output of cleanImageByEdge
+ * (HypothesisEvaluation.h:384): both tightly packed, so pixel (x, y) is element y * w + x whatever x is
+ * (x == w wraps into the next row); `stride` only says where the caller keeps row yy of that image. */
 static int pixel_err(const uint8_t* bgr, const uint8_t* mask, int w, int h, int stride, int x, int y, const int* des)
 {
-    (void)w;
-    long off = (long)y * stride + 3L * x;
+    long pix = (long)y * w + x;
     int b = 0, g = 0, r = 0;
-    if (off >= 0 && off + 2 < (long)stride * h) {
+    if (pix >= 0 && pix < (long)w * h) {
+        long yy = pix / w, xx = pix - yy * w;
         int keep = 1;
-        if (mask) { /* cleaned image = img.copyTo(out, mask): tightly packed, stride == 3w */
-            long pix = off / 3;
-            keep = mask[pix] != 0;
+        if (mask) keep = mask[pix] != 0;
+        if (keep) {
+            const uint8_t* p = bgr + yy * stride + 3 * xx;
+            b = p[0]; g = p[1]; r = p[2];
         }
-        if (keep) { b = bgr[off]; g = bgr[off + 1]; r = bgr[off + 2]; }
     }
     int db = b - des[0], dg = g - des[1], dr = r - des[2];
     return db * db + dg * dg + dr * dr;

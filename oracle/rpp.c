@@ -11,7 +11,7 @@
  *
  * Validation: against the reference's own RPP.cpp/Rpoly.cpp compiled into
  * oracle/_ref/librpp_ref.so (oracle/ref_build/Makefile) and against the known-answer vector
- * of RobustPlanarPose/demo.cpp:17-38, by tests/test_oracle_rpp.py.
+ * of RobustPlanarPose/demo.cpp:17-38, by tests/test_oracle_parts.py.
  */
 #include "mantis_oracle.h"
 #include <math.h>

@@ -50,3 +50,18 @@ def test_product_does_not_import_oracle():
                 text = open(os.path.join(dp, fn)).read()
                 for pat in (r"^\s*(from|import)\s+oracle", r"#include\s*[<\"].*oracle", r"libmantis_oracle", r"pyoracle"):
                     assert not re.search(pat, text, flags=re.M), f"{fn} uses the oracle ({pat})"
+
+
+def test_create_rejects_bad_config_before_touching_a_device():
+    """mantis_create validates mantis_config up front: limits the kernels are built for and
+    non-finite / non-positive tunables come back as MANTIS_ERR_INVALID (-1), never as a CUDA error later."""
+    lib = mantis_b200.load_library()
+    bad = []
+    for field, value in (("particles", 97), ("particles", -1), ("iterations", -3), ("iterations", 1 << 30), ("grid_size", 10),
+                         ("grid_size", 0), ("grid_spacing", 0.0), ("grid_spacing", float("nan")), ("projection_bias", -1.0),
+                         ("color_projection_bias", float("inf")), ("rot_sigma", -0.1), ("canny_hysteresis", 100000)):
+        cfg = mantis_b200.binding.default_config()
+        setattr(cfg, field, value)
+        h = ctypes.c_void_p()
+        bad.append((field, value, lib.mantis_create(ctypes.byref(cfg), 0, ctypes.byref(h)), h.value))
+    assert all(rc == -1 and handle is None for _, _, rc, handle in bad), bad

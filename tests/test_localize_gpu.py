@@ -209,3 +209,35 @@ def test_localize_capacity_limits_are_reported(ctx):
     for i in (1, 2):
         assert res[i].status == 4 and tr[i].flags != 0
         assert res[i].error == 0 and all(v == 0 for v in res[i].pos[:])
+
+
+def test_localize_small_grid_keeps_reference_order():
+    """grid_size = 4 gives 16 cell shifts: getBestNHypotheses(20) then returns the list UNSORTED
+    (HypothesisEvaluation.h:492), so hyps.back() is the last shift, not the best."""
+    import mantis_b200
+
+    K, D = K_for(640, 480), np.zeros(4)
+    frames = np.stack([po.render_grid(R, t, K, D, 640, 480) for R, t in poses(4, seed=0x4D414E54 + 13)])
+    cfg = mantis_b200.binding.default_config()
+    cfg.grid_size = 4
+    prm = po.default_params()
+    prm.grid_size = 4
+    with mantis_b200.Context(0, cfg) as c:
+        res, tr = c.localize(frames, K, D, want_trace=True)
+    for i in range(len(frames)):
+        otr, _ = po.localize(frames[i], K, D, params=prm)
+        assert list(tr[i].shift_err[:16]) == list(otr.shift_err[:16])
+        assert tr[i].best_rot == otr.best_rot
+        assert np.allclose(list(tr[i].yaw_err), list(otr.yaw_err), rtol=1e-12)
+        assert np.abs(np.array(res[i].pos[:]) - np.array(otr.pos[:])).max() < 1e-3
+        assert rot_angle(np.array(res[i].quat_xyzw[:]), np.array(otr.quat_xyzw[:])) < 1e-4
+        assert res[i].error == pytest.approx(otr.error, rel=1e-12)
+
+
+def test_localize_rejects_skewed_camera_matrix(ctx):
+    import mantis_b200
+
+    K = K_for(64, 48).copy()
+    K[0, 1] = 0.5
+    with pytest.raises(mantis_b200.MantisError, match="skew"):
+        ctx.localize(np.zeros((1, 48, 64, 3), np.uint8), K, np.zeros(4))

@@ -14,7 +14,7 @@ from oracle import pyoracle as po
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def quads_via_cv2(cv2, img, T=50, eps=10, mult=0.1):
+def quads_via_cv2(cv2, img, T=50, eps=10, mult=0.1, flann=False):
     mono = cv2.GaussianBlur(cv2.cvtColor(img, cv2.COLOR_BGR2GRAY), (3, 3), 3, 3)
     canny = cv2.Canny(mono, T, 3 * T, apertureSize=3)
     canny = cv2.erode(cv2.dilate(canny, None, iterations=2), None, iterations=1)
@@ -35,10 +35,23 @@ def quads_via_cv2(cv2, img, T=50, eps=10, mult=0.1):
         cen.append((f32(xs / f32(4)), f32(ys / f32(4))))
     side = [np.sqrt(float((q[0][0] - q[1][0]) ** 2 + (q[0][1] - q[1][1]) ** 2)) for q in quads]
     neighbor = [False] * n_raw
+    tree = None
+    if flann and n_raw:
+        # the reference's own call (QuadDetection.h:130,143): KD-tree with one tree, radiusSearch(query, indices, dists,
+        # radius, 4).  Its fresh std::vector<int> is resized to 4 zero-initialised entries by OpenCV, which the
+        # zero-filled output arrays reproduce; FLANN writes only the hits.
+        feats = np.array(cen, np.float32).reshape(-1, 2)
+        tree = cv2.flann_Index(feats, dict(algorithm=1, trees=1))
     for e in range(n_raw):
         if neighbor[e]:
             continue
         rad = f32(mult * side[e])
+        if tree is not None:
+            ind, dst = np.zeros((1, 4), np.int32), np.zeros((1, 4), np.float32)
+            tree.radiusSearch(np.array([cen[e]], np.float32), float(mult * side[e]), 4, ind, dst)
+            for j in ind[0, 1:]:
+                neighbor[int(j)] = True
+            continue
         d = [f32(f32((cen[e][0] - c[0]) * (cen[e][0] - c[0])) + f32((cen[e][1] - c[1]) * (cen[e][1] - c[1]))) for c in cen]
         hits = sorted([(d[j], j) for j in range(n_raw) if d[j] <= rad])[:4]
         idx = [j for _, j in hits] + [0] * (4 - len(hits))
@@ -59,6 +72,27 @@ def test_quads_match_cv2(name):
         assert list(tr.quad_corners[i]) == q.reshape(-1).tolist()
     if name == "grid1":
         assert (n_cont, n_raw) == (142, 24)  # SURVEY section 4 golden counts
+
+
+@pytest.mark.parametrize("name", ["grid1", "lena", "blocky_720x1280", "blocky_1080x1920", "grid_a", "grid_b", "grid_c", "grid_d"])
+def test_duplicate_removal_matches_cv2_flann(name):
+    """removeDuplicateQuads through the real cv::flann::Index (KDTreeIndexParams(1), radiusSearch, maxResults 4):
+    which quads survive -- hit order, the squared-radius comparison and the 'unfilled slots are index 0' quirk
+    included -- must be what the oracle's exact search keeps."""
+    cv2 = pytest.importorskip("cv2")
+    if name.startswith("grid_"):
+        K, D = K_for(640, 480), np.zeros(4)
+        R, t = poses(4, seed=0x4D414E54 + 31)["abcd".index(name[-1])]
+        img = po.render_grid(R, t, K, D, 640, 480)
+        tr, _ = po.localize(img, K, D)
+    else:
+        img = all_cases()[name]
+        tr, _ = po.localize(img, K_GRID1, D_UNIT)
+    n_raw, keep, n_cont = quads_via_cv2(cv2, img, flann=True)
+    assert (tr.n_contours, tr.n_quads_raw) == (n_cont, n_raw)
+    assert tr.n_quads == len(keep)
+    for i, q in enumerate(keep):
+        assert list(tr.quad_corners[i]) == q.reshape(-1).tolist()
 
 
 def score_white_numpy(cv2, hyp_c2w_R, hyp_c2w_t, img, mask, K, D, maps):
