@@ -204,6 +204,43 @@ int mantis_pnp_batch(mantis_ctx* ctx, const float* obj_xyz, const float* img_xy,
                      mantis_pnp_result* out, int mem);
 
 /*
+ * Planar pose from point correspondences, batched: RPP::Rpp(model_3D, iprts, rotation, translation, iterations,
+ * obj_err, img_err) (include/mantis3/RobustPlanarPose/RPP.h:54-55, RPP.cpp:13-64) as called per quad by
+ * CoPlanarPoseEstimator::estimatePose (CoPlanarPoseEstimator.cpp:16-58).
+ *   model_xyz   m x (x, y, z) doubles per problem (one shared set when model_shared != 0)
+ *   image_xy    m x (x, y) doubles per problem: NORMALISED image points (the reference passes z = 1 rows)
+ *   m           3 .. 16 points.  Planar 4-point problems (z == 0: every quad of the localization path) run through
+ *               the very kernels of mantis_localize_batch; other shapes through the general 3x3-SVD form.
+ * img_err carries the reference's quirk (every point compared with image point 0, RPP.cpp:197-198): it is the
+ * quantity generateCentralHypotheses gates on (HypothesisGeneration.h:80).
+ */
+enum { MANTIS_RPP_OK = 0, MANTIS_RPP_FAILED = 1 };  /* FAILED: RPP::Rpp returned false (no second-pose candidate) */
+typedef struct mantis_rpp_result {
+    double R[9];            /* rotation (row-major) and translation: p_camera = R p_model + t */
+    double t[3];
+    double obj_err, img_err;
+    int32_t iters_first;    /* AbsKernel calls of the first ObjPose run (RPP.cpp:66-208); -1 = not recorded */
+    int32_t iters_best;     /* ... of the refinement run that won */
+    int32_t n_candidates;   /* second-pose candidates refined (Get2ndPose_Exact, RPP.cpp:693-753) */
+    int32_t status;
+} mantis_rpp_result;
+int mantis_rpp_batch(mantis_ctx* ctx, const double* model_xyz, int model_shared, const double* image_xy, int n, int m,
+                     mantis_rpp_result* out, int mem);
+
+/*
+ * Map-correspondence score of given poses on given frames, batched: evaluateHypothesisWithImageWHITE on the image
+ * cleanImageByEdge produces (include/mantis3/HypothesisEvaluation.h:107-158, 319-386) -- steps (5) + (6) of
+ * quadDetection() for caller-supplied hypotheses, through the scoring loop of mantis_localize_batch.
+ *   K, D      9 floats + 4 doubles per frame (as in mantis_frame)
+ *   w2c       n x n_hyps x 12 doubles: R row-major + t of each hypothesis' W2C (what Hypothesis::setW2C receives)
+ *   scores    n x n_hyps doubles: sum of squared colour distances to WHITE / (projected points x PROJECTION_BIAS),
+ *             DBL_MAX when no map point projects into the frame
+ */
+int mantis_score_batch(mantis_ctx* ctx, const uint8_t* bgr, int n, int width, int height, int stride_bytes,
+                       size_t frame_pitch_bytes, const float* K, const double* D, const double* w2c, int n_hyps,
+                       double* scores, int mem);
+
+/*
  * Whole-frame localization: everything quadDetection() does between receiving the image and
  * calling publishPose() (src/mantis3.cpp:68-135).
  */

@@ -16,6 +16,7 @@ from .binding import (  # noqa: F401
     FrameQuads,
     FrameTrace,
     Result,
+    RppResult,
     MantisError,
     PnpResult,
     build_library,

@@ -119,6 +119,14 @@ class PnpResult(ctypes.Structure):
                 ("passes", ctypes.c_int32), ("status", ctypes.c_int32)]
 
 
+class RppResult(ctypes.Structure):
+    """mantis_rpp_result."""
+
+    _fields_ = [("R", ctypes.c_double * 9), ("t", ctypes.c_double * 3), ("obj_err", ctypes.c_double),
+                ("img_err", ctypes.c_double), ("iters_first", ctypes.c_int32), ("iters_best", ctypes.c_int32),
+                ("n_candidates", ctypes.c_int32), ("status", ctypes.c_int32)]
+
+
 PNP_BOTH_PLANAR = 1
 NOALLOC_SCRATCH_BYTES = 8 << 20  # MANTIS_NOALLOC_SCRATCH_BYTES
 
@@ -184,6 +192,9 @@ def load_library():
                                              c.c_int, c.c_size_t]
     lib.mantis_degrade_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t,
                                          c.c_int, c.c_size_t, c.c_float, c.c_float, c.c_uint32]
+    lib.mantis_rpp_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_int, c.c_int, c.c_void_p, c.c_int]
+    lib.mantis_score_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t, c.c_void_p,
+                                       c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_int]
     lib.mantis_edges_noalloc.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_int, c.c_size_t, c.c_void_p,
                                          c.c_void_p]
     lib.mantis_set_profiling.argtypes = [c.c_void_p, c.c_int]
@@ -340,6 +351,38 @@ class Context:
         rc = self._lib.mantis_pnp_batch(self._h, _ptr(d_obj), _ptr(d_img), n, m, int(obj_shared), _ptr(d_K), int(k_shared),
                                         _ptr(d_guess), ctypes.byref(prm), _ptr(d_out), MEM_DEVICE)
         self._check(rc, "mantis_pnp_batch")
+
+    # -- RPP::Rpp per problem, RobustPlanarPose/RPP.h:54-55 (CoPlanarPoseEstimator.cpp:16-58) --
+    def rpp(self, model_xyz, image_xy):
+        """model_xyz [n,m,3] or [m,3] (shared), image_xy [n,m,2] normalised image points -> (RppResult * n)."""
+        model = np.ascontiguousarray(model_xyz, np.float64)
+        img = np.ascontiguousarray(image_xy, np.float64)
+        n, m, _ = img.shape
+        out = (RppResult * n)()
+        rc = self._lib.mantis_rpp_batch(self._h, _ptr(model), int(model.ndim == 2), _ptr(img), n, m, ctypes.addressof(out),
+                                        MEM_HOST)
+        self._check(rc, "mantis_rpp_batch")
+        return out
+
+    # -- evaluateHypothesisWithImageWHITE on cleanImageByEdge's image, HypothesisEvaluation.h:107-158, 319-386 --
+    def score(self, bgr, K, D, w2c):
+        """bgr [n,H,W,3], K [3,3] or [n,3,3], D [4] or [n,4], w2c [n,P,12] (R row-major + t) -> scores [n,P]."""
+        bgr = np.ascontiguousarray(bgr, np.uint8)
+        if bgr.ndim == 3:
+            bgr = bgr[None]
+        n, h, w, _ = bgr.shape
+        K = np.ascontiguousarray(K, np.float32)
+        if K.ndim == 2:
+            K = np.repeat(K[None], n, 0)
+        D = np.ascontiguousarray(D, np.float64)
+        if D.ndim == 1:
+            D = np.repeat(D[None], n, 0)
+        w2c = np.ascontiguousarray(w2c, np.float64).reshape(n, -1, 12)
+        out = np.zeros((n, w2c.shape[1]), np.float64)
+        rc = self._lib.mantis_score_batch(self._h, _ptr(bgr), n, w, h, 3 * w, 3 * w * h, _ptr(K), _ptr(D), _ptr(w2c),
+                                          w2c.shape[1], _ptr(out), MEM_HOST)
+        self._check(rc, "mantis_score_batch")
+        return out
 
     # -- 2016 generation: computeCameraError / undistortImage, legacy/mantis/MonteCarlo.cpp:169-241,284 --
     def particle_weights(self, bgr, K, w2c):

@@ -127,6 +127,12 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
 int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n,
                   int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
                   const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace);
+int launch_rpp_planar4(mantis_ctx* c, const double* d_model_xyz, int model_shared, const double* d_image_xy, int n,
+                       mantis_rpp_result* d_out);
+int launch_rpp_generic(mantis_ctx* c, const double* d_model_xyz, int model_shared, const double* d_image_xy, int n, int m,
+                       mantis_rpp_result* d_out);
+int launch_score(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n, int w,
+                 int h, const pm::Camera* d_cams, const double* d_w2c, int n_hyps, double* d_scores);
 extern "C" int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int height, int stride_bytes,
                    size_t frame_pitch_bytes, const EdgeOutputs& out);
 

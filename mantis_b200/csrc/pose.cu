@@ -18,6 +18,7 @@ constexpr int PNT = 128;
 
 struct RunOut {   // result of one ObjPose run
     double R[9], t[3], obj_err, img_err;
+    int calls, pad_;  // AbsKernel calls of the run (the reference's `it`, RPP.cpp:66-208)
 };
 
 struct PoseCounters {   // zeroed before every batch
@@ -44,6 +45,7 @@ struct PoseArgs {
     double* candR;           // [cap * 2 * 4][9]
     RunOut* run2;            // [cap * 2 * 4]
     int cap;
+    const double* models;    // stage-level entry (mantis_rpp_batch) only: [cap][8] planar model (x, y) per quad; null = the grid square
     long long* dbg;          // tuning aid (null = off): slots 10..15 = AbsKernel steps spent in runs of <16, <64, <256, <1024, <4096, more steps
     double half_spacing, max_quad_error, cluster_radius;
     Tf rotz;                 // tf::Transform(tf::Quaternion(0, 0, 1/sqrt2, 1/sqrt2))
@@ -119,7 +121,8 @@ __global__ void __launch_bounds__(RNT, RUN_CTAS) k_pose_run(PoseArgs a, int roun
                         task = list[my];
                         const int entry = HAS_INIT ? (task >> 2) : task;
                         double m[8];
-                        model_xy(a.half_spacing, entry & 1, m);
+                        if (a.models) { for (int k = 0; k < 8; ++k) m[k] = a.models[(size_t)(entry >> 1) * 8 + k]; }
+                        else model_xy(a.half_spacing, entry & 1, m);
                         rppf::setup(ctx, RNT, a.rays + (size_t)(entry >> 1) * 8, m, L);
                         rppf::run_begin(ctx, RNT, L, S, HAS_INIT ? a.candR + (size_t)task * 9 : nullptr);
                     } else {
@@ -133,6 +136,8 @@ __global__ void __launch_bounds__(RNT, RUN_CTAS) k_pose_run(PoseArgs a, int roun
             if (a.dbg && !HAS_INIT) atomicAdd((unsigned long long*)&a.dbg[10 + (S.it >= 16) + (S.it >= 64) + (S.it >= 256) + (S.it >= 1024) + (S.it >= 4096)], (unsigned long long)S.it);
             RunOut o;
             rppf::finalize(ctx, RNT, L, o.R, o.t, o.obj_err, o.img_err);
+            o.calls = S.it + (HAS_INIT ? 1 : 2);
+            o.pad_ = 0;
             out[task] = o;
             task = -1;
         }
@@ -150,7 +155,8 @@ __global__ void __launch_bounds__(PNT, SECOND_CTAS) k_pose_second(PoseArgs a, in
     for (int i = blockIdx.x * PNT + threadIdx.x; i < ntask; i += gridDim.x * PNT) {
         const int entry = list[i];
         double m[8];
-        model_xy(a.half_spacing, entry & 1, m);
+        if (a.models) { for (int k = 0; k < 8; ++k) m[k] = a.models[(size_t)(entry >> 1) * 8 + k]; }
+        else model_xy(a.half_spacing, entry & 1, m);
         pm::V3 model[4], ray[4];
         for (int k = 0; k < 4; ++k) {
             model[k].v[0] = m[2 * k]; model[k].v[1] = m[2 * k + 1]; model[k].v[2] = 0;
@@ -331,6 +337,74 @@ __global__ void __launch_bounds__(PNT) k_pose_cluster(PoseArgs a)
     }
 }
 
+// ---- stage-level entry (mantis_rpp_batch): n planar 4-point problems through the kernels above -------------
+// One queue entry per problem (entry = 2 * problem: "ordering 0" slot, the model comes from a.models).
+__global__ void __launch_bounds__(PNT) k_rpp_stage_prep(PoseArgs a, const double* model_xyz, int model_shared, const double* image_xy,
+                                                        int n, double* models_out)
+{
+    const int i = blockIdx.x * PNT + threadIdx.x;
+    if (i == 0) a.cnt->n_t1[0] = n;
+    if (i >= n) return;
+    const double* mp = model_xyz + (model_shared ? 0 : (size_t)i * 12);
+    for (int k = 0; k < 4; ++k) {
+        models_out[(size_t)i * 8 + 2 * k] = mp[3 * k];
+        models_out[(size_t)i * 8 + 2 * k + 1] = mp[3 * k + 1];
+        a.rays[(size_t)i * 8 + 2 * k] = image_xy[(size_t)i * 8 + 2 * k];
+        a.rays[(size_t)i * 8 + 2 * k + 1] = image_xy[(size_t)i * 8 + 2 * k + 1];
+    }
+    a.list1[i] = 2 * i;
+}
+
+// RPP::Rpp's choice among the refined candidates (RPP.cpp:36-52): lowest object-space error, first wins ties.
+__global__ void __launch_bounds__(PNT) k_rpp_stage_gather(PoseArgs a, int n, mantis_rpp_result* out)
+{
+    const int i = blockIdx.x * PNT + threadIdx.x;
+    if (i >= n) return;
+    const int entry = 2 * i, ns = a.ncand[entry];
+    mantis_rpp_result r;
+    for (int k = 0; k < 9; ++k) r.R[k] = 0;
+    for (int k = 0; k < 3; ++k) r.t[k] = 0;
+    r.obj_err = r.img_err = 0;
+    r.iters_first = a.run1[entry].calls;
+    r.iters_best = 0;
+    r.n_candidates = ns > 0 ? ns : 0;
+    r.status = MANTIS_RPP_FAILED;
+    int best = -1;
+    double lowest = 1e6;
+    for (int cnd = 0; cnd < ns; ++cnd) {
+        const double oe = a.run2[(size_t)entry * 4 + cnd].obj_err;
+        if (oe < lowest) { lowest = oe; best = cnd; }
+    }
+    if (best >= 0) {
+        const RunOut& b = a.run2[(size_t)entry * 4 + best];
+        for (int k = 0; k < 9; ++k) r.R[k] = b.R[k];
+        for (int k = 0; k < 3; ++k) r.t[k] = b.t[k];
+        r.obj_err = b.obj_err; r.img_err = b.img_err;
+        r.iters_best = b.calls;
+        r.status = MANTIS_RPP_OK;
+    }
+    out[i] = r;
+}
+
+// Workspace of the ObjPose queue for `cap` quads, carved out of one context buffer.
+int pose_workspace(mantis_ctx* c, size_t cap, PoseArgs& a)
+{
+    a.cap = (int)cap;
+    a.models = nullptr;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
+    const size_t o_cnt = take(sizeof(PoseCounters)), o_rays = take(cap * 8 * sizeof(double)), o_l1 = take(cap * 2 * sizeof(int)),
+                 o_l2 = take(cap * 8 * sizeof(int)), o_run1 = take(cap * 2 * sizeof(RunOut)), o_nc = take(cap * 2 * sizeof(int)),
+                 o_cr = take(cap * 8 * 9 * sizeof(double)), o_run2 = take(cap * 8 * sizeof(RunOut));
+    int rc;
+    if ((rc = ctx_reserve(c, c->pose_offs, o))) return rc;
+    char* ws = (char*)c->pose_offs.p;
+    a.cnt = (PoseCounters*)(ws + o_cnt); a.rays = (double*)(ws + o_rays); a.list1 = (int*)(ws + o_l1);
+    a.list2 = (int*)(ws + o_l2); a.run1 = (RunOut*)(ws + o_run1); a.ncand = (int*)(ws + o_nc);
+    a.candR = (double*)(ws + o_cr); a.run2 = (RunOut*)(ws + o_run2);
+    return MANTIS_OK;
+}
+
 }  // namespace
 
 int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_cams, int n, Hyp* d_hyps, short* d_sel,
@@ -342,20 +416,10 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
     a.max_quad_error = c->cfg.max_quad_error;
     a.cluster_radius = c->cfg.max_angle_difference;
     a.rotz = c->rotz;
-    const size_t cap = (size_t)n * MANTIS_MAX_QUADS;
-    a.cap = (int)cap;
-    size_t o = 0;
-    auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
-    const size_t o_cnt = take(sizeof(PoseCounters)), o_rays = take(cap * 8 * sizeof(double)), o_l1 = take(cap * 2 * sizeof(int)),
-                 o_l2 = take(cap * 8 * sizeof(int)), o_run1 = take(cap * 2 * sizeof(RunOut)), o_nc = take(cap * 2 * sizeof(int)),
-                 o_cr = take(cap * 8 * 9 * sizeof(double)), o_run2 = take(cap * 8 * sizeof(RunOut));
     int rc;
-    if ((rc = ctx_reserve(c, c->quad_hyp, cap * sizeof(Hyp))) || (rc = ctx_reserve(c, c->pose_offs, o))) return rc;
-    char* ws = (char*)c->pose_offs.p;
+    if ((rc = pose_workspace(c, (size_t)n * MANTIS_MAX_QUADS, a))) return rc;
+    if ((rc = ctx_reserve(c, c->quad_hyp, (size_t)a.cap * sizeof(Hyp)))) return rc;
     a.quad_hyp = (Hyp*)c->quad_hyp.p;
-    a.cnt = (PoseCounters*)(ws + o_cnt); a.rays = (double*)(ws + o_rays); a.list1 = (int*)(ws + o_l1);
-    a.list2 = (int*)(ws + o_l2); a.run1 = (RunOut*)(ws + o_run1); a.ncand = (int*)(ws + o_nc);
-    a.candR = (double*)(ws + o_cr); a.run2 = (RunOut*)(ws + o_run2);
     a.dbg = (long long*)c->dbg_clocks;
     MCHECK(c, cudaMemsetAsync(a.cnt, 0, sizeof(PoseCounters), c->stream));
     k_pose_prep<<<n, PNT, 0, c->stream>>>(a);
@@ -370,6 +434,37 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
     k_pose_select<<<flat_blocks, PNT, 0, c->stream>>>(a, 0);
     k_pose_cluster<<<n, PNT, 0, c->stream>>>(a);
     c->launches += 6;
+    MCHECK(c, cudaGetLastError());
+    return MANTIS_OK;
+}
+
+// n planar 4-point problems (device pointers) through k_pose_run / k_pose_second, the kernels of the localization path.
+int launch_rpp_planar4(mantis_ctx* c, const double* d_model_xyz, int model_shared, const double* d_image_xy, int n,
+                       mantis_rpp_result* d_out)
+{
+    PoseArgs a;
+    a.quads = nullptr; a.cams = nullptr; a.n_frames = 0; a.hyps = nullptr; a.sel = nullptr; a.info = nullptr; a.quad_hyp = nullptr;
+    a.half_spacing = c->cfg.grid_spacing / 2;
+    a.max_quad_error = c->cfg.max_quad_error;
+    a.cluster_radius = c->cfg.max_angle_difference;
+    a.rotz = c->rotz;
+    int rc;
+    if ((rc = pose_workspace(c, (size_t)n, a))) return rc;
+    if ((rc = ctx_reserve(c, c->quad_hyp, (size_t)n * 8 * sizeof(double)))) return rc;   // (free here: holds the models)
+    a.models = (const double*)c->quad_hyp.p;
+    a.dbg = nullptr;
+    MCHECK(c, cudaMemsetAsync(a.cnt, 0, sizeof(PoseCounters), c->stream));
+    const int flat = (n + PNT - 1) / PNT;
+    k_rpp_stage_prep<<<flat, PNT, 0, c->stream>>>(a, d_model_xyz, model_shared, d_image_xy, n, (double*)c->quad_hyp.p);
+    const int run_blocks = c->sm_count * 4;
+    const int run_smem = rppf::CTX_WORDS * RNT * (int)sizeof(double);
+    MCHECK(c, cudaFuncSetAttribute(k_pose_run<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, run_smem));
+    MCHECK(c, cudaFuncSetAttribute(k_pose_run<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, run_smem));
+    k_pose_run<false><<<run_blocks, RNT, run_smem, c->stream>>>(a, 0);
+    k_pose_second<<<c->sm_count * SECOND_CTAS * 2, PNT, 0, c->stream>>>(a, 0);
+    k_pose_run<true><<<run_blocks, RNT, run_smem, c->stream>>>(a, 0);
+    k_rpp_stage_gather<<<flat, PNT, 0, c->stream>>>(a, n, d_out);
+    c->launches += 5;
     MCHECK(c, cudaGetLastError());
     return MANTIS_OK;
 }

@@ -141,10 +141,10 @@ struct ObjCtx {
 };
 
 template <int N>
-__device__ inline V3 estimate_t(const ObjCtx<N>& c, const M3& R)
+__device__ inline V3 estimate_t(const ObjCtx<N>& c, const M3& R, int n = N)
 {
     V3 sum = {{0, 0, 0}};
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         V3 x = pm::mulv(c.F[i], pm::mulv(R, c.P[i]));
         for (int k = 0; k < 3; ++k) sum.v[k] += x.v[k];
     }
@@ -152,12 +152,12 @@ __device__ inline V3 estimate_t(const ObjCtx<N>& c, const M3& R)
 }
 
 template <int N>
-__device__ inline void abs_kernel(const ObjCtx<N>& c, V3* Q, M3& R, V3& t, double& err2)
+__device__ inline void abs_kernel(const ObjCtx<N>& c, V3* Q, M3& R, V3& t, double& err2, int n = N)
 {
-    for (int i = 0; i < N; ++i) Q[i] = pm::mulv(c.F[i], Q[i]);
+    for (int i = 0; i < n; ++i) Q[i] = pm::mulv(c.F[i], Q[i]);
     M3 M;
     for (int k = 0; k < 9; ++k) M.m[k] = 0;
-    for (int i = 0; i < N; ++i)
+    for (int i = 0; i < n; ++i)
         for (int a = 0; a < 3; ++a)
             for (int b = 0; b < 3; ++b) M.m[a * 3 + b] += c.P[i].v[a] * Q[i].v[b];
     M3 U, V;
@@ -166,24 +166,24 @@ __device__ inline void abs_kernel(const ObjCtx<N>& c, V3* Q, M3& R, V3& t, doubl
     M3 Ut = pm::transpose(U);
     R = pm::mul(V, Ut);
     if (pm::det(R) > 0) {
-        t = estimate_t(c, R);
+        t = estimate_t(c, R, n);
         if (t.v[2] < 0) {
             for (int k = 0; k < 3; ++k) V.m[k * 3 + 2] = -V.m[k * 3 + 2];
             R = pm::mul(V, Ut);
             for (int k = 0; k < 9; ++k) R.m[k] = -R.m[k];
-            t = estimate_t(c, R);
+            t = estimate_t(c, R, n);
         }
     } else {
         for (int k = 0; k < 3; ++k) V.m[k * 3 + 2] = -V.m[k * 3 + 2];
         R = pm::mul(V, Ut);
-        t = estimate_t(c, R);
+        t = estimate_t(c, R, n);
         if (t.v[2] < 0) {
             for (int k = 0; k < 9; ++k) R.m[k] = -R.m[k];
-            t = estimate_t(c, R);
+            t = estimate_t(c, R, n);
         }
     }
     err2 = 0;
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         V3 q = pm::mulv(R, c.P[i]);
         for (int k = 0; k < 3; ++k) q.v[k] += t.v[k];
         Q[i] = q;
@@ -194,16 +194,16 @@ __device__ inline void abs_kernel(const ObjCtx<N>& c, V3* Q, M3& R, V3& t, doubl
 
 // model / rays: N points, model[i] = (x, y, z), ray[i] = (x, y, 1)
 template <int N>
-__device__ inline void setup(ObjCtx<N>& c, const V3* model, const V3* ray)
+__device__ inline void setup(ObjCtx<N>& c, const V3* model, const V3* ray, int n = N)
 {
     for (int k = 0; k < 3; ++k) {
         double s = 0;
-        for (int i = 0; i < N; ++i) s += model[i].v[k];
-        c.pbar.v[k] = s / N;
+        for (int i = 0; i < n; ++i) s += model[i].v[k];
+        c.pbar.v[k] = s / n;
     }
     M3 sumF;
     for (int k = 0; k < 9; ++k) sumF.m[k] = 0;
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         for (int k = 0; k < 3; ++k) {
             c.P[i].v[k] = model[i].v[k] - c.pbar.v[k];
             c.Qp[i].v[k] = ray[i].v[k];
@@ -217,14 +217,14 @@ __device__ inline void setup(ObjCtx<N>& c, const V3* model, const V3* ray)
             }
     }
     M3 A = pm::eye();
-    for (int k = 0; k < 9; ++k) A.m[k] -= sumF.m[k] / N;
+    for (int k = 0; k < 9; ++k) A.m[k] -= sumF.m[k] / n;
     c.tF = pm::inverse(A);
-    for (int k = 0; k < 9; ++k) c.tF.m[k] /= N;
+    for (int k = 0; k < 9; ++k) c.tF.m[k] /= n;
 }
 
 template <int N>
 __device__ inline void obj_pose(const ObjCtx<N>& c, bool has_init, const M3& initR, M3& Rout, V3& tout, double& obj_err,
-                                double& img_err)
+                                double& img_err, int* calls = nullptr, int n = N)
 {
     const double TOL = 1e-5, EPSILON = 1e-8;
     V3 Q[N];
@@ -235,14 +235,14 @@ __device__ inline void obj_pose(const ObjCtx<N>& c, bool has_init, const M3& ini
     if (has_init) {
         Ri = initR;
         V3 sum = {{0, 0, 0}};
-        for (int i = 0; i < N; ++i) {
+        for (int i = 0; i < n; ++i) {
             V3 rp = pm::mulv(Ri, c.P[i]);
             V3 frp = pm::mulv(c.F[i], rp);
             for (int k = 0; k < 3; ++k) sum.v[k] += frp.v[k] - rp.v[k];
         }
         ti = pm::mulv(c.tF, sum);
         old_err = 0;
-        for (int i = 0; i < N; ++i) {
+        for (int i = 0; i < n; ++i) {
             V3 q = pm::mulv(Ri, c.P[i]);
             for (int k = 0; k < 3; ++k) q.v[k] += ti.v[k];
             Q[i] = q;
@@ -250,21 +250,22 @@ __device__ inline void obj_pose(const ObjCtx<N>& c, bool has_init, const M3& ini
             for (int k = 0; k < 3; ++k) { double e = q.v[k] - fq.v[k]; old_err += e * e; }
         }
     } else {
-        for (int i = 0; i < N; ++i) Q[i] = c.Qp[i];
-        abs_kernel(c, Q, Ri, ti, old_err);
+        for (int i = 0; i < n; ++i) Q[i] = c.Qp[i];
+        abs_kernel(c, Q, Ri, ti, old_err, n);
         it = 1;
     }
-    abs_kernel(c, Q, Ri, ti, new_err);
+    abs_kernel(c, Q, Ri, ti, new_err, n);
     it += 1;
     while (fabs((old_err - new_err) / old_err) > TOL && new_err > EPSILON) {
         old_err = new_err;
-        abs_kernel(c, Q, Ri, ti, new_err);
+        abs_kernel(c, Q, Ri, ti, new_err, n);
         if (++it > 100000) break;
     }
+    if (calls) *calls = it;
     Rout = Ri;
-    obj_err = sqrt(new_err / N);
+    obj_err = sqrt(new_err / n);
     double ie = 0;
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         V3 q = pm::mulv(Ri, c.P[i]);
         for (int k = 0; k < 3; ++k) q.v[k] += ti.v[k];
         // reference quirk (RPP.cpp:197-198): every point is compared with image point 0
@@ -272,7 +273,7 @@ __device__ inline void obj_pose(const ObjCtx<N>& c, bool has_init, const M3& ini
         double yy = q.v[1] / q.v[2] - c.Qp[0].v[1];
         ie += xx * xx + yy * yy;
     }
-    img_err = sqrt(ie / N);
+    img_err = sqrt(ie / n);
     V3 rp = pm::mulv(Ri, c.pbar);
     for (int k = 0; k < 3; ++k) tout.v[k] = ti.v[k] - rp.v[k];
 }

@@ -4,12 +4,12 @@ namespace rpp {
 // RPP::GetRotationY_wrtT (RPP.cpp:947-1222): minima of the object-space error over the rotation
 // beta about y, and the optimal translation for each.
 template <int N>
-__device__ inline int rotation_y_wrt_t(const V3* v, const V3* p, const M3& Rz, double* bl, V3* tnew)
+__device__ inline int rotation_y_wrt_t(const V3* v, const V3* p, const M3& Rz, double* bl, V3* tnew, int n = N)
 {
     const double PI = 3.14159265358979323846;
     M3 Vp[N], G, I = pm::eye();
     for (int k = 0; k < 9; ++k) G.m[k] = 0;
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         double vv = v[i].v[0] * v[i].v[0] + v[i].v[1] * v[i].v[1] + v[i].v[2] * v[i].v[2];
         for (int a = 0; a < 3; ++a)
             for (int b = 0; b < 3; ++b) {
@@ -17,13 +17,13 @@ __device__ inline int rotation_y_wrt_t(const V3* v, const V3* p, const M3& Rz, d
                 G.m[a * 3 + b] += Vp[i].m[a * 3 + b];
             }
     }
-    for (int k = 0; k < 9; ++k) G.m[k] = I.m[k] - G.m[k] / N;
+    for (int k = 0; k < 9; ++k) G.m[k] = I.m[k] - G.m[k] / n;
     G = pm::inverse(G);
-    for (int k = 0; k < 9; ++k) G.m[k] /= N;
+    for (int k = 0; k < 9; ++k) G.m[k] /= n;
 
     M3 opt_t;
     for (int k = 0; k < 9; ++k) opt_t.m[k] = 0;
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         double px = p[i].v[0], py = p[i].v[1], pz = p[i].v[2];
         M3 Rpi = {{-px, 2 * pz, px, py, 0, py, -pz, -2 * px, pz}};
         M3 A;
@@ -34,7 +34,7 @@ __device__ inline int rotation_y_wrt_t(const V3* v, const V3* p, const M3& Rz, d
     opt_t = pm::mul(G, opt_t);
 
     double E2[5] = {0, 0, 0, 0, 0};
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         double px = p[i].v[0], py = p[i].v[1], pz = p[i].v[2];
         M3 Rpi = {{-px, 2 * pz, px, py, 0, py, -pz, -2 * px, pz}};
         M3 A, S = pm::mul(Rz, Rpi);
@@ -65,7 +65,7 @@ __device__ inline int rotation_y_wrt_t(const V3* v, const V3* p, const M3& Rz, d
         double beta = al_deg * PI / 180;  // the reference round-trips through degrees
         M3 R = pm::mul(Rz, rpy_mat(0, beta, 0));
         V3 topt = {{0, 0, 0}};
-        for (int k = 0; k < N; ++k) {
+        for (int k = 0; k < n; ++k) {
             V3 rp = pm::mulv(R, p[k]);
             V3 vrp = pm::mulv(Vp[k], rp);
             for (int q = 0; q < 3; ++q) topt.v[q] += vrp.v[q] - rp.v[q];
@@ -80,11 +80,11 @@ __device__ inline int rotation_y_wrt_t(const V3* v, const V3* p, const M3& Rz, d
 // RPP::Get2ndPose_Exact + GetRfor2ndPose_V_Exact + DecomposeR: candidate second poses.
 // Returns the number of candidates, or -1 where the reference returns false.
 template <int N>
-__device__ inline int second_poses(const V3* model, const V3* ray, const M3& R, M3* solR, V3* solT)
+__device__ inline int second_poses(const V3* model, const V3* ray, const M3& R, M3* solR, V3* solT, int n = N)
 {
     const double PI = 3.14159265358979323846;
     V3 cent = {{0, 0, 0}};
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < n; ++i) {
         double x = ray[i].v[0], y = ray[i].v[1], z = ray[i].v[2];
         double m = 1.0 / sqrt(x * x + y * y + z * z);
         cent.v[0] += x * m; cent.v[1] += y * m; cent.v[2] += z * m;
@@ -108,7 +108,7 @@ __device__ inline int second_poses(const V3* model, const V3* ray, const M3& R, 
     Rim.m[6] = 2 * (qb * qd - qa * qc); Rim.m[7] = 2 * (qc * qd + qa * qb); Rim.m[8] = qa * qa + qd * qd - qb * qb - qc * qc;
 
     V3 v_[N];
-    for (int i = 0; i < N; ++i) v_[i] = pm::mulv(Rim, ray[i]);
+    for (int i = 0; i < n; ++i) v_[i] = pm::mulv(Rim, ray[i]);
     M3 R_ = pm::mul(Rim, R);
 
     // DecomposeR
@@ -126,13 +126,13 @@ __device__ inline int second_poses(const V3* model, const V3* ray, const M3& R, 
 
     M3 RzNt = pm::transpose(RzN);
     V3 P_[N];
-    for (int i = 0; i < N; ++i) P_[i] = pm::mulv(RzNt, model[i]);
+    for (int i = 0; i < n; ++i) P_[i] = pm::mulv(RzNt, model[i]);
     if (!rpy_ang_x(Rt, ang)) return -1;
     M3 Rz = rpy_mat(0, 0, ang[2]);
 
     double bl[4];
     V3 tnew[4];
-    int ns = rotation_y_wrt_t<N>(v_, P_, Rz, bl, tnew);
+    int ns = rotation_y_wrt_t<N>(v_, P_, Rz, bl, tnew, n);
     if (ns == 0) return -1;
     M3 Rimt = pm::transpose(Rim);
     for (int j = 0; j < ns; ++j) {
@@ -144,26 +144,33 @@ __device__ inline int second_poses(const V3* model, const V3* ray, const M3& R, 
 }
 
 // RPP::Rpp.  Returns false where the reference returns false (or indexes sol[-1]).
+// its (optional): AbsKernel calls of the first run, of the winning refinement run, and the number of candidates.
 template <int N>
-__device__ inline bool solve(const V3* model, const V3* ray, M3& R, V3& t, double& obj_err, double& img_err)
+__device__ inline bool solve(const V3* model, const V3* ray, M3& R, V3& t, double& obj_err, double& img_err, int* its = nullptr, int n = N)
 {
     ObjCtx<N> c;
-    setup<N>(c, model, ray);
+    setup<N>(c, model, ray, n);
     M3 Rlu;
     V3 tlu;
     double oe, ie;
-    obj_pose<N>(c, false, pm::eye(), Rlu, tlu, oe, ie);
+    int calls = 0;
+    obj_pose<N>(c, false, pm::eye(), Rlu, tlu, oe, ie, &calls, n);
+    if (its) { its[0] = calls; its[1] = 0; its[2] = 0; }
     M3 solR[4];
     V3 solT[4];
-    int ns = second_poses<N>(model, ray, Rlu, solR, solT);
+    int ns = second_poses<N>(model, ray, Rlu, solR, solT, n);
     if (ns <= 0) return false;
+    if (its) its[2] = ns;
     int best = -1;
     double lowest = 1e6;
     for (int i = 0; i < ns; ++i) {
         M3 Ri;
         V3 ti;
-        obj_pose<N>(c, true, solR[i], Ri, ti, oe, ie);
-        if (oe < lowest) { lowest = oe; best = i; R = Ri; t = ti; obj_err = oe; img_err = ie; }
+        obj_pose<N>(c, true, solR[i], Ri, ti, oe, ie, &calls, n);
+        if (oe < lowest) {
+            lowest = oe; best = i; R = Ri; t = ti; obj_err = oe; img_err = ie;
+            if (its) its[1] = calls;
+        }
     }
     return best >= 0;
 }

@@ -153,6 +153,10 @@ struct SearchArgs {
     mantis_result* out;
     mantis_frame_trace* trace;  // may be null
     long long* dbg;             // tuning aid: clock64 per phase (null = off)
+    // score-only mode (mantis_score_batch): ext_n caller-supplied poses per frame instead of the search
+    const double* ext_w2c;      // [n][ext_n][12] R row-major + t, what Hypothesis::setW2C receives; null = search
+    double* ext_scores;         // [n][ext_n]
+    int ext_n;
 };
 
 // What the scoring loop needs about the frame, in shared memory: every use is one broadcast LDS, which is
@@ -366,13 +370,14 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
     __syncthreads();
     const int frame = s.frame;
     if (frame >= a.n) break;
-    mantis_result* out = a.out + frame;
-    mantis_frame_trace* tr = a.trace ? a.trace + frame : nullptr;
-    const FrameQuads* fq = a.quads + frame;
-    const FramePose* info = a.info + frame;
-    const int n_sel = info->n_sel;
+    const bool ext = a.ext_w2c != nullptr;
+    mantis_result* out = ext ? nullptr : a.out + frame;
+    mantis_frame_trace* tr = (!ext && a.trace) ? a.trace + frame : nullptr;
+    const FrameQuads* fq = ext ? nullptr : a.quads + frame;
+    const FramePose* info = ext ? nullptr : a.info + frame;
+    const int n_sel = ext ? 0 : info->n_sel;
 
-    if (tid == 0) {
+    if (tid == 0 && !ext) {
         out->n_quads = fq->n_quads;
         out->n_hyps = n_sel;
         out->n_particles = 0;
@@ -388,7 +393,7 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
             tr->best_rot = -1; tr->pad_ = 0;
         }
     }
-    if (fq->flags || fq->n_quads == 0 || n_sel == 0) continue;
+    if (!ext && (fq->flags || fq->n_quads == 0 || n_sel == 0)) continue;
 
     if (tid == 0) {
         s.img.bgr = a.bgr + (size_t)frame * a.pitch;
@@ -430,6 +435,36 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
     auto tick = [&](int slot) {
         if (a.dbg && tid == 0) { long long t = clock64(); atomicAdd((unsigned long long*)&a.dbg[slot], (unsigned long long)(t - tk)); tk = t; }
     };
+
+    if (ext) {
+        // evaluateHypothesisWithImageWHITE (HypothesisEvaluation.h:107-158) for the caller's poses, through the same
+        // scoring loop as the search, 96 poses at a time
+        const int mode_e = (planar ? 2 : 0) | (cam.has_dist ? 1 : 0);
+        for (int base = 0; base < a.ext_n; base += 96) {
+            const int nh = min(96, a.ext_n - base);
+            __syncthreads();
+            if (tid < nh) {
+                const double* src = a.ext_w2c + ((size_t)frame * a.ext_n + base + tid) * 12;
+                Tf w;
+                for (int k = 0; k < 9; ++k) w.R[k] = src[k];
+                for (int k = 0; k < 3; ++k) w.t[k] = src[9 + k];
+                s.cand_w2c[tid] = w;
+                pm::tf_inv(w, s.cand_c2w[tid]);
+            }
+            for (int i = tid; i < nh; i += SNT) { s.sum[i] = 0ull; s.cnt[i] = 0; }
+            __syncthreads();
+            const char* tfb = reinterpret_cast<const char*>(s.cand_c2w);
+            if (mode_e == 2) score_loop<true, false>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+            else if (mode_e == 3) score_loop<true, true>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+            else if (mode_e == 0) score_loop<false, false>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+            else score_loop<false, true>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+            __syncthreads();
+            for (int i = tid; i < nh; i += SNT)
+                a.ext_scores[(size_t)frame * a.ext_n + base + i] =
+                    s.cnt[i] > 0 ? (double)s.sum[i] / ((double)s.cnt[i] * a.projection_bias) : DBLMAX;
+        }
+        continue;
+    }
 
     // Phases of the search, all through ONE inlined copy of the scoring loop:
     //   0                 (6) evaluateHypotheses on the kept cluster, (7) best 1
@@ -651,9 +686,10 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
 
 }  // namespace
 
-int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n,
-                  int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
-                  const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace)
+static int launch_search_impl(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n,
+                              int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
+                              const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace,
+                              const double* d_ext_w2c, int ext_n, double* d_ext_scores)
 {
     if (c->n_map <= 0 || c->n_map > MAX_MAP || c->n_green > 40 || c->n_shift > 96 || c->cfg.particles > 96) {
         snprintf(c->err, sizeof(c->err), "map / search sizes exceed the kernel's limits (map %d, green %d)", c->n_map, c->n_green);
@@ -677,6 +713,7 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
     a.color_bias = c->cfg.color_projection_bias;
     a.out = d_out; a.trace = d_trace;
     a.dbg = (long long*)c->dbg_clocks;
+    a.ext_w2c = d_ext_w2c; a.ext_n = ext_n; a.ext_scores = d_ext_scores;
     // persistent CTAs (one per SM); frames come from a ticket counter
     const int grid = n < c->sm_count ? n : c->sm_count;
     int rc = ctx_reserve(c, c->search_ticket, sizeof(unsigned));
@@ -697,4 +734,20 @@ int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride,
     c->launches++;
     MCHECK(c, cudaGetLastError());
     return MANTIS_OK;
+}
+
+int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n,
+                  int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
+                  const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace)
+{
+    return launch_search_impl(c, d_bgr, pitch, stride, d_mask_bits, n, w, h, d_cams, d_quads, d_hyps, d_sel, d_info, d_out,
+                              d_trace, nullptr, 0, nullptr);
+}
+
+// Score-only launch: WHITE scores of n_hyps caller-supplied poses per frame on the masked image.
+int launch_score(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n, int w,
+                 int h, const pm::Camera* d_cams, const double* d_w2c, int n_hyps, double* d_scores)
+{
+    return launch_search_impl(c, d_bgr, pitch, stride, d_mask_bits, n, w, h, d_cams, nullptr, nullptr, nullptr, nullptr, nullptr,
+                              nullptr, d_w2c, n_hyps, d_scores);
 }

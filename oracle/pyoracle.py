@@ -274,6 +274,28 @@ def localize(bgr, K, D, params=None, maps=None, want_mask=False):
     return tr, mask
 
 
+def score_white(w2c12, bgr, K, D, maps=None, bias=1.1):
+    """evaluateHypothesisWithImageWHITE on cleanImageByEdge's image (HypothesisEvaluation.h:107-158, 319-386) for the
+    hypothesis whose W2C is w2c12 (R row-major + t)."""
+    bgr, p = _u8(bgr)
+    h, w, _ = bgr.shape
+    K = np.ascontiguousarray(K, np.float32)
+    D = np.ascontiguousarray(D, np.float64)
+    can, _m = edge_stage(bgr, 50)
+    mask = clean_mask(can)
+    tf = _Tf()
+    v = np.asarray(w2c12, np.float64).reshape(-1)
+    tf.R[:] = v[:9].tolist()
+    tf.t[:] = v[9:].tolist()
+    hyp = _Hyp()
+    lib().mo_hyp_set_w2c(ctypes.byref(hyp), ctypes.byref(tf))
+    lib().mo_score_white.restype = ctypes.c_double
+    lib().mo_score_white.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                     ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double]
+    return lib().mo_score_white(ctypes.byref(hyp), p, mask.ctypes.data, w, h, 3 * w, K.ctypes.data, D.ctypes.data,
+                                ctypes.addressof(_map_struct(maps)), float(bias))
+
+
 def clean_mask(canny):
     canny, p = _u8(canny)
     h, w = canny.shape
