@@ -249,7 +249,7 @@ typedef struct mantis_frame {     /* one sensor_msgs/Image + CameraInfo of manti
     int32_t width, height, stride_bytes;
     float K[9];                   /* CameraInfo.K as the CV_32F 3x3 of get3x3FromVector, QuadDetection.h:189-201; K[1] (skew) must be 0 */
     double D[4];                  /* CameraInfo.D, fisheye coefficients (src/mantis3.cpp:74) */
-    double cam_to_base[7];        /* optional camera->base_link transform (x y z qx qy qz qw); identity if qw==0 */
+    double cam_to_base[7];        /* camera->base_link transform (x y z qx qy qz qw), read by mantis_localize_rig_batch; all-zero quaternion = identity */
     uint64_t stamp_ns;
     int32_t camera_id;
 } mantis_frame;
@@ -290,6 +290,24 @@ int mantis_set_map(mantis_ctx* ctx, const double* xyz, int n_white, int n_red, i
  * out[n] (and the optional trace[n]) are host arrays. */
 int mantis_localize_batch(mantis_ctx* ctx, const mantis_frame* frames, int n, mantis_result* out,
                           mantis_frame_trace* trace, int mem);
+
+/*
+ * Rigs: joint multi-camera localization (BASELINE.json configs[2]).  frames holds n_rigs x cams_per_rig records, the
+ * cameras of a rig next to each other, each with its cam_to_base -- the per-camera base->camera transform of the
+ * reference's requests (tf::StampedTransform b2c, include/legacy/mantis/MantisRequest.h:14-26).  Every camera runs
+ * steps (1)-(3) of quadDetection() on its own image; its hypotheses are moved to the BASE frame
+ * (W2B = W2C_k * b2c_k^-1) and pooled; from the clustering on, a hypothesis is a base pose and every score is the
+ * joint one the reference states as its intent: camera k sees W2C_k = W2B * b2c_k (new_hyp.setW2C(hyp.getW2C() * b2c),
+ * include/legacy/mantis2/Mantis2Error.h:67-68), colour errors and projected-point counts run on over the cameras
+ * (computeImageError's `projected`, :55-99; MonteCarlo::computeWeight leaves the second camera as a TODO,
+ * include/legacy/mantis/MonteCarlo.cpp:233-241).  Refinement, cell shifts and the yaw decision act on the base pose.
+ * out / trace: one record per RIG (pose of the base in the world; n_quads etc. summed over the cameras).  A rig of one
+ * camera at the base origin gives mantis_localize_batch's record.  The pooled hypotheses of a rig share the capacity
+ * cams_per_rig x 1024.
+ */
+#define MANTIS_MAX_RIG_CAMERAS 8
+int mantis_localize_rig_batch(mantis_ctx* ctx, const mantis_frame* frames, int n_rigs, int cams_per_rig, mantis_result* out,
+                              mantis_frame_trace* trace, int mem);
 
 /*
  * The 2016 generation's particle weight, batched over particles x frames:

@@ -187,6 +187,7 @@ def load_library():
                                                 c.c_int, c.c_int]
     lib.mantis_set_map.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int]
     lib.mantis_localize_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_localize_rig_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_render_grid_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p,
                                              c.c_void_p, c.c_double, c.c_int, c.c_float, c.c_uint32, c.c_void_p,
                                              c.c_int, c.c_size_t]
@@ -463,6 +464,37 @@ class Context:
         n, h, w, _ = bgr.shape
         frames = self.make_frames([bgr[i] for i in range(n)], w, h, K, D)
         return self.localize_frames(frames, MEM_HOST, want_trace)
+
+    # -- rigs: joint multi-camera localization (MantisRequest.h:14-26, Mantis2Error.h:55-99) --
+    def localize_rig(self, bgr, Ks, Ds, cam_to_base, want_trace=False):
+        """bgr [R, C, H, W, 3] (R rigs of C cameras) on the host; Ks [C,3,3], Ds [C,4], cam_to_base [C,7]
+        (x y z qx qy qz qw of each camera in the base frame) shared by all rigs.  One Result per rig (base pose)."""
+        bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+        if bgr.ndim == 4:
+            bgr = bgr[None]
+        R, C, h, w, _ = bgr.shape
+        fr = (Frame * (R * C))()
+        Ks = np.ascontiguousarray(Ks, np.float32).reshape(C, 9)
+        Ds = np.ascontiguousarray(Ds, np.float64).reshape(C, 4)
+        b2c = np.ascontiguousarray(cam_to_base, np.float64).reshape(C, 7)
+        for r in range(R):
+            for k in range(C):
+                f = fr[r * C + k]
+                f.bgr = bgr[r, k].ctypes.data
+                f.width, f.height, f.stride_bytes = w, h, 3 * w
+                f.K[:] = Ks[k].tolist()
+                f.D[:] = Ds[k].tolist()
+                f.cam_to_base[:] = b2c[k].tolist()
+                f.camera_id = k
+        return self.localize_rig_frames(fr, R, C, MEM_HOST, want_trace)
+
+    def localize_rig_frames(self, frames, n_rigs, cams_per_rig, mem, want_trace=False):
+        out = (Result * n_rigs)()
+        tr = (FrameTrace * n_rigs)() if want_trace else None
+        rc = self._lib.mantis_localize_rig_batch(self._h, ctypes.addressof(frames), n_rigs, cams_per_rig, ctypes.addressof(out),
+                                                 ctypes.addressof(tr) if want_trace else None, mem)
+        self._check(rc, "mantis_localize_rig_batch")
+        return out, tr
 
     def localize_frames(self, frames, mem, want_trace=False):
         n = len(frames)

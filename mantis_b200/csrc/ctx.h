@@ -50,6 +50,7 @@ struct mantis_ctx {
     int map_planar = 0;                      // every map point has z == 0 (the reference's floor grid)
     DevBuf d_atan;                           // (i pi/256, tan(i pi/256)) table of the fast fp64 atan (search.cu)
     Tf rotz;                                 // +90 degrees about z
+    DevBuf rig_tf;                           // rigs: per frame b2c and its inverse (localize.cu)
     DevBuf search_ticket;                    // k_search: frame ticket counter of the persistent CTAs
     DevBuf stage_in, stage_in2, stage_out0, stage_out1;  // device staging for MANTIS_MEM_HOST callers
     cudaStream_t copy_stream = nullptr;       // H2D of the next chunk while the current one computes
@@ -122,8 +123,10 @@ int launch_edge_link(mantis_ctx* c, const uint32_t* d_weak, const uint32_t* d_st
 int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int h, mantis_frame_quads* d_out);
 
 namespace pm { struct Camera; }
+// cams_per_unit > 1 (or d_b2c_inv != null): the frames are rigs of cams_per_unit cameras whose hypotheses are pooled
+// in the base frame (per-frame d_b2c_inv); n must be a multiple of cams_per_unit.
 int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_cams, int n, Hyp* d_hyps, short* d_sel,
-                FramePose* d_info);
+                FramePose* d_info, int cams_per_unit = 1, const Tf* d_b2c_inv = nullptr);
 int launch_search(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n,
                   int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
                   const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace);
@@ -131,6 +134,10 @@ int launch_rpp_planar4(mantis_ctx* c, const double* d_model_xyz, int model_share
                        mantis_rpp_result* d_out);
 int launch_rpp_generic(mantis_ctx* c, const double* d_model_xyz, int model_shared, const double* d_image_xy, int n, int m,
                        mantis_rpp_result* d_out);
+int launch_search_rig(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n_rigs,
+                      int rig_cams, int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
+                      const short* d_sel, const FramePose* d_info, const Tf* d_b2c, mantis_result* d_out,
+                      mantis_frame_trace* d_trace);
 int launch_score(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n, int w,
                  int h, const pm::Camera* d_cams, const double* d_w2c, int n_hyps, double* d_scores);
 extern "C" int run_edge_stage(mantis_ctx* c, const uint8_t* d_in, int n, int width, int height, int stride_bytes,

@@ -105,12 +105,17 @@ extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int
     return MANTIS_OK;
 }
 
-extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, int n, mantis_result* out,
-                                     mantis_frame_trace* trace, int mem)
+// quadDetection() for n frames.  rig_cams == 0: every frame on its own (mantis_localize_batch).  rig_cams >= 1: the frames
+// are rigs of rig_cams cameras localized jointly through their cam_to_base (mantis_localize_rig_batch); out / trace then
+// hold one record per rig.
+static int localize_impl(mantis_ctx* c, const mantis_frame* frames, int n, mantis_result* out, mantis_frame_trace* trace,
+                         int mem, int rig_cams)
 {
     if (!c || n < 0 || (n > 0 && (!frames || !out)) || (mem != MANTIS_MEM_HOST && mem != MANTIS_MEM_DEVICE))
         return MANTIS_ERR_INVALID;
     if (n == 0) return MANTIS_OK;
+    const bool rig = rig_cams > 0;
+    const int UC = rig ? rig_cams : 1;   // frames per unit of output
     const int W = frames[0].width, H = frames[0].height, stride0 = frames[0].stride_bytes;
     if (W <= 0 || H <= 0 || W > 32767 || H > 32767 || stride0 < 3 * W) return MANTIS_ERR_INVALID;
     for (int i = 0; i < n; ++i)
@@ -141,7 +146,7 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     // frames for 1 / 2 / 3 lanes), so the default is 1.  Per-stage profiling always uses the single-lane path.
     static const int lanes_env = []() { const char* e = getenv("MANTIS_LANES"); return e ? atoi(e) : 1; }();
     const int L = lanes_env > mantis_ctx::MAX_LANES ? mantis_ctx::MAX_LANES : lanes_env;
-    if (mem == MANTIS_MEM_DEVICE && !c->is_lane && !c->profiling && L >= 2 && n >= 512 * L) {
+    if (!rig && mem == MANTIS_MEM_DEVICE && !c->is_lane && !c->profiling && L >= 2 && n >= 512 * L) {
         for (int i = 0; i < L; ++i)
             if (!c->lane[i]) {
                 int rc0 = mantis_create(&c->cfg, c->device, &c->lane[i]);
@@ -175,6 +180,8 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     // kernels of a chunk finish before the next copy does, and that the LAST chunk -- the only one whose kernels are
     // not hidden -- is short: 512-frame chunks, the final one split once more.
     if (mem == MANTIS_MEM_HOST && chunk_env <= 0 && CHUNK > 512) CHUNK = 512;
+    CHUNK = CHUNK / UC * UC;             // whole rigs per chunk
+    if (CHUNK < UC) CHUNK = UC;
     const int WW = words_per_row(W);
     const int nc_max = n < CHUNK ? n : CHUNK;
     const size_t plane_bytes = (size_t)nc_max * H * WW * sizeof(uint32_t);
@@ -212,7 +219,7 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
     for (int f0 = 0; f0 < n; f0 += CHUNK) {
         start.push_back(f0);
         const int nc = (n - f0 < CHUNK) ? (n - f0) : CHUNK;
-        if (mem == MANTIS_MEM_HOST && f0 + CHUNK >= n && f0 > 0 && nc >= 256) start.push_back(f0 + nc / 2);
+        if (mem == MANTIS_MEM_HOST && f0 + CHUNK >= n && f0 > 0 && nc >= 256) start.push_back(f0 + nc / 2 / UC * UC);
     }
     start.push_back(n);
     const int n_chunks = (int)start.size() - 1;
@@ -231,6 +238,7 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         return MANTIS_OK;
     };
     std::vector<pm::Camera> cams((size_t)nc_max);
+    std::vector<Tf> rig_tf;
     // The chunk loop as one unit: whatever makes it stop early, no copy may still be reading the caller's frames
     // (or writing the caller's results) once this call has returned.
     auto run_chunks = [&]() -> int {
@@ -259,6 +267,27 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
             for (int k = 0; k < 4; ++k) cm.D[k] = f.D[k];
         }
         MCHECK(c, cudaMemcpyAsync(c->cams.p, cams.data(), sizeof(pm::Camera) * (size_t)nc, cudaMemcpyHostToDevice, c->stream));
+        const Tf* d_b2c = nullptr;
+        const Tf* d_b2c_inv = nullptr;
+        if (rig) {   // per frame: the camera in the base frame (MantisRequest.h:14-26's b2c) and its inverse
+            rig_tf.resize(2 * (size_t)nc);
+            for (int i = 0; i < nc; ++i) {
+                const double* q = frames[f0 + i].cam_to_base;
+                Tf& b = rig_tf[i];
+                if (q[3] == 0 && q[4] == 0 && q[5] == 0 && q[6] == 0) {   // not given: the camera is the base
+                    for (int k = 0; k < 9; ++k) b.R[k] = (k % 4 == 0) ? 1.0 : 0.0;
+                    b.t[0] = b.t[1] = b.t[2] = 0;
+                } else {
+                    pm::quat_to_mat(q + 3, b.R);
+                    for (int k = 0; k < 3; ++k) b.t[k] = q[k];
+                }
+                pm::tf_inv(b, rig_tf[(size_t)nc + i]);
+            }
+            if ((rc = ctx_reserve(c, c->rig_tf, sizeof(Tf) * 2 * (size_t)nc_max))) return rc;
+            MCHECK(c, cudaMemcpyAsync(c->rig_tf.p, rig_tf.data(), sizeof(Tf) * 2 * (size_t)nc, cudaMemcpyHostToDevice, c->stream));
+            d_b2c = (const Tf*)c->rig_tf.p;
+            d_b2c_inv = d_b2c + nc;
+        }
 
         prof_mark(c, 1);
         EdgeOutputs eo;
@@ -270,19 +299,26 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         if ((rc = launch_quads(c, eo.morph_bits, nc, W, H, (FrameQuads*)c->frame_quads.p))) return rc;
         prof_mark(c, 4);
         if ((rc = launch_pose(c, (const FrameQuads*)c->frame_quads.p, (const pm::Camera*)c->cams.p, nc, (Hyp*)c->hyps.p,
-                              (short*)c->sel.p, (FramePose*)c->pose_info.p)))
+                              (short*)c->sel.p, (FramePose*)c->pose_info.p, UC, d_b2c_inv)))
             return rc;
         prof_mark(c, 5);
-        if ((rc = launch_search(c, d_in, pitch, stride, eo.mask_bits, nc, W, H, (const pm::Camera*)c->cams.p,
-                                (const FrameQuads*)c->frame_quads.p, (const Hyp*)c->hyps.p, (const short*)c->sel.p,
-                                (const FramePose*)c->pose_info.p, (mantis_result*)c->results.p,
-                                trace ? (mantis_frame_trace*)c->traces.p : nullptr)))
-            return rc;
+        if (rig)
+            rc = launch_search_rig(c, d_in, pitch, stride, eo.mask_bits, nc / UC, UC, W, H, (const pm::Camera*)c->cams.p,
+                                   (const FrameQuads*)c->frame_quads.p, (const Hyp*)c->hyps.p, (const short*)c->sel.p,
+                                   (const FramePose*)c->pose_info.p, d_b2c, (mantis_result*)c->results.p,
+                                   trace ? (mantis_frame_trace*)c->traces.p : nullptr);
+        else
+            rc = launch_search(c, d_in, pitch, stride, eo.mask_bits, nc, W, H, (const pm::Camera*)c->cams.p,
+                               (const FrameQuads*)c->frame_quads.p, (const Hyp*)c->hyps.p, (const short*)c->sel.p,
+                               (const FramePose*)c->pose_info.p, (mantis_result*)c->results.p,
+                               trace ? (mantis_frame_trace*)c->traces.p : nullptr);
+        if (rc) return rc;
         prof_mark(c, 6);
         if (host) MCHECK(c, cudaEventRecord(c->ev_free[k & 1], c->stream));
-        MCHECK(c, cudaMemcpyAsync(out + f0, c->results.p, sizeof(mantis_result) * (size_t)nc, cudaMemcpyDeviceToHost, c->stream));
+        MCHECK(c, cudaMemcpyAsync(out + f0 / UC, c->results.p, sizeof(mantis_result) * (size_t)(nc / UC), cudaMemcpyDeviceToHost,
+                                  c->stream));
         if (trace)
-            MCHECK(c, cudaMemcpyAsync(trace + f0, c->traces.p, sizeof(mantis_frame_trace) * (size_t)nc,
+            MCHECK(c, cudaMemcpyAsync(trace + f0 / UC, c->traces.p, sizeof(mantis_frame_trace) * (size_t)(nc / UC),
                                       cudaMemcpyDeviceToHost, c->stream));
         prof_mark(c, 7);
         MCHECK(c, cudaStreamSynchronize(c->stream));
@@ -296,4 +332,18 @@ extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, 
         cudaStreamSynchronize(c->stream);
     }
     return rc;
+}
+
+extern "C" int mantis_localize_batch(mantis_ctx* c, const mantis_frame* frames, int n, mantis_result* out,
+                                     mantis_frame_trace* trace, int mem)
+{
+    return localize_impl(c, frames, n, out, trace, mem, 0);
+}
+
+extern "C" int mantis_localize_rig_batch(mantis_ctx* c, const mantis_frame* frames, int n_rigs, int cams_per_rig,
+                                         mantis_result* out, mantis_frame_trace* trace, int mem)
+{
+    if (cams_per_rig < 1 || cams_per_rig > MANTIS_MAX_RIG_CAMERAS || n_rigs < 0 || (long long)n_rigs * cams_per_rig > 0x7fffffffLL)
+        return MANTIS_ERR_INVALID;
+    return localize_impl(c, frames, n_rigs * cams_per_rig, out, trace, mem, cams_per_rig);
 }

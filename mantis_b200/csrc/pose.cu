@@ -45,6 +45,8 @@ struct PoseArgs {
     double* candR;           // [cap * 2 * 4][9]
     RunOut* run2;            // [cap * 2 * 4]
     int cap;
+    int cams_per_unit;       // 1, or the cameras of a rig (k_pose_cluster pools their hypotheses)
+    const Tf* b2c_inv;       // rigs only: per frame, base <- camera inverted; null = hypotheses stay camera poses
     const double* models;    // stage-level entry (mantis_rpp_batch) only: [cap][8] planar model (x, y) per quad; null = the grid square
     long long* dbg;          // tuning aid (null = off): slots 10..15 = AbsKernel steps spent in runs of <16, <64, <256, <1024, <4096, more steps
     double half_spacing, max_quad_error, cluster_radius;
@@ -225,47 +227,70 @@ __global__ void __launch_bounds__(PNT) k_pose_select(PoseArgs a, int round)
 
 // Per frame: hypotheses of the passing quads in quad order (4 yaw copies each), Euler angles,
 // greedy clustering, largest cluster.
+// A unit is one frame, or -- for a rig (mantis_localize_rig_batch) -- the a.cams_per_unit consecutive frames of one rig:
+// then every camera's hypotheses are moved to the base frame (W2B = W2C_k * b2c_k^-1, the inverse of
+// Mantis2Error.h:67-68's setW2C(hyp.getW2C() * b2c)) and pooled in camera order before the clustering.  The unit's
+// pool / selection live in the slots of its first frame onwards (capacity cams_per_unit * MANTIS_MAX_HYPS); its
+// totals (n_hyps_generated, n_sel) go to the FramePose of its first frame.
 __global__ void __launch_bounds__(PNT) k_pose_cluster(PoseArgs a)
 {
-    __shared__ float s_ang[MANTIS_MAX_HYPS][3];
-    __shared__ unsigned char s_taken[MANTIS_MAX_HYPS];
-    __shared__ unsigned char s_member[MANTIS_MAX_HYPS];
-    __shared__ unsigned char s_best[MANTIS_MAX_HYPS];
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    const int C = a.cams_per_unit, cap = C * MANTIS_MAX_HYPS;
+    float (*s_ang)[3] = reinterpret_cast<float (*)[3]>(s_dyn);
+    unsigned char* s_taken = s_dyn + (size_t)cap * 3 * sizeof(float);
+    unsigned char* s_member = s_taken + cap;
+    unsigned char* s_best = s_member + cap;
     __shared__ short s_slot[MANTIS_MAX_QUADS];
     __shared__ float s_center[3];
     __shared__ int s_cnt, s_nh;
 
-    const int frame = blockIdx.x, tid = threadIdx.x;
-    const FrameQuads* fq = a.quads + frame;
-    Hyp* hyps = a.hyps + (size_t)frame * MANTIS_MAX_HYPS;
-    short* sel = a.sel + (size_t)frame * MANTIS_MAX_HYPS;
-    FramePose* info = a.info + frame;
-    const int nq = fq->n_quads;
-
-    if (tid == 0) {
-        int acc = 0;
-        for (int k = 0; k < nq; ++k) { s_slot[k] = (short)acc; acc += info->quad_pass[k] ? 1 : 0; }
-        s_nh = acc;
-    }
-    __syncthreads();
-    for (int q = tid; q < nq; q += PNT) {
-        if (!info->quad_pass[q]) continue;
-        Hyp hk = a.quad_hyp[(size_t)frame * MANTIS_MAX_QUADS + q];
-        const int base = 4 * s_slot[q];
-        hyps[base] = hk;
-        for (int k = 1; k < 4; ++k) {
-            Tf w2c;
-            pm::tf_mul(a.rotz, hk.w2c, w2c);
-            pm::hyp_set_w2c(hk, w2c);
-            hyps[base + k] = hk;
+    const int unit = blockIdx.x, tid = threadIdx.x;
+    Hyp* hyps = a.hyps + (size_t)unit * cap;
+    short* sel = a.sel + (size_t)unit * cap;
+    FramePose* info = a.info + (size_t)unit * C;   // the unit's totals
+    int nq_total = 0, nh_total = 0;
+    for (int cam = 0; cam < C; ++cam) {
+        const int frame = unit * C + cam;
+        const FrameQuads* fq = a.quads + frame;
+        const FramePose* finfo = a.info + frame;
+        const int nq = fq->flags ? 0 : fq->n_quads;
+        __syncthreads();
+        if (tid == 0) {
+            int acc = 0;
+            for (int k = 0; k < nq; ++k) { s_slot[k] = (short)acc; acc += finfo->quad_pass[k] ? 1 : 0; }
+            s_nh = acc;
         }
+        __syncthreads();
+        for (int q = tid; q < nq; q += PNT) {
+            if (!finfo->quad_pass[q]) continue;
+            Hyp hk = a.quad_hyp[(size_t)frame * MANTIS_MAX_QUADS + q];
+            const int base = nh_total + 4 * s_slot[q];
+            for (int k = 0; k < 4; ++k) {
+                if (k > 0) {
+                    Tf w2c;
+                    pm::tf_mul(a.rotz, hk.w2c, w2c);
+                    pm::hyp_set_w2c(hk, w2c);
+                }
+                if (a.b2c_inv) {   // camera pose -> base pose
+                    Hyp hb = hk;
+                    Tf w2b;
+                    pm::tf_mul(hk.w2c, a.b2c_inv[frame], w2b);
+                    pm::hyp_set_w2c(hb, w2b);
+                    hyps[base + k] = hb;
+                } else {
+                    hyps[base + k] = hk;
+                }
+            }
+        }
+        nq_total += nq;
+        nh_total += 4 * s_nh;
     }
     __syncthreads();
-    if (nq == 0) {
+    if (nq_total == 0) {
         if (tid == 0) { info->n_hyps_generated = 0; info->n_sel = 0; }
         return;
     }
-    const int nh = 4 * s_nh;
+    const int nh = nh_total;
 
     // ---- Euler angles (tf::Matrix3x3(q).getRPY, stored as float like cv::Point3f) ----
     for (int i = tid; i < nh; i += PNT) {
@@ -391,6 +416,8 @@ int pose_workspace(mantis_ctx* c, size_t cap, PoseArgs& a)
 {
     a.cap = (int)cap;
     a.models = nullptr;
+    a.cams_per_unit = 1;
+    a.b2c_inv = nullptr;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
     const size_t o_cnt = take(sizeof(PoseCounters)), o_rays = take(cap * 8 * sizeof(double)), o_l1 = take(cap * 2 * sizeof(int)),
@@ -408,7 +435,7 @@ int pose_workspace(mantis_ctx* c, size_t cap, PoseArgs& a)
 }  // namespace
 
 int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_cams, int n, Hyp* d_hyps, short* d_sel,
-                FramePose* d_info)
+                FramePose* d_info, int cams_per_unit, const Tf* d_b2c_inv)
 {
     PoseArgs a;
     a.quads = d_quads; a.cams = d_cams; a.n_frames = n; a.hyps = d_hyps; a.sel = d_sel; a.info = d_info;
@@ -432,7 +459,11 @@ int launch_pose(mantis_ctx* c, const FrameQuads* d_quads, const pm::Camera* d_ca
     k_pose_second<<<c->sm_count * SECOND_CTAS * 2, PNT, 0, c->stream>>>(a, 0);
     k_pose_run<true><<<run_blocks, RNT, run_smem, c->stream>>>(a, 0);
     k_pose_select<<<flat_blocks, PNT, 0, c->stream>>>(a, 0);
-    k_pose_cluster<<<n, PNT, 0, c->stream>>>(a);
+    a.cams_per_unit = cams_per_unit;
+    a.b2c_inv = d_b2c_inv;
+    const int cluster_smem = cams_per_unit * MANTIS_MAX_HYPS * (3 * (int)sizeof(float) + 3);
+    MCHECK(c, cudaFuncSetAttribute(k_pose_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, cluster_smem));
+    k_pose_cluster<<<n / cams_per_unit, PNT, cluster_smem, c->stream>>>(a);
     c->launches += 6;
     MCHECK(c, cudaGetLastError());
     return MANTIS_OK;

@@ -154,6 +154,9 @@ struct SearchArgs {
     mantis_frame_trace* trace;  // may be null
     long long* dbg;             // tuning aid: clock64 per phase (null = off)
     // score-only mode (mantis_score_batch): ext_n caller-supplied poses per frame instead of the search
+    // rigs (k_search_rig): a unit is C consecutive frames; hypotheses are base poses, camera k sees W2B * b2c[frame]
+    int C;
+    const Tf* b2c;              // per frame: the camera in the base frame (mantis_frame.cam_to_base)
     const double* ext_w2c;      // [n][ext_n][12] R row-major + t, what Hypothesis::setW2C receives; null = search
     double* ext_scores;         // [n][ext_n]
     int ext_n;
@@ -684,12 +687,273 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
     }  // frame loop
 }
 
+
+// The scoring loop as a function of its own for k_search_rig: compiled apart from the kernel around it (that kernel
+// keeps poses and camera models in local memory between calls; inlined into it the loop spilled and mis-scored).
+__device__ __noinline__ void score_loop_call(Shared& s, const SearchArgs& a, int nh, int mode)
+{
+    const char* tfb = reinterpret_cast<const char*>(s.cand_c2w);
+    if (mode == 2) score_loop<true, false>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+    else if (mode == 3) score_loop<true, true>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+    else if (mode == 0) score_loop<false, false>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+    else score_loop<false, true>(s, a, nh, tfb, (int)sizeof(Tf), nullptr);
+}
+
+// ---- rigs: the same search on the JOINT score of the C cameras of a rig --------------------------------------------
+// A hypothesis is the pose of the base; camera k sees it as W2C_k = W2B * b2c_k (include/legacy/mantis2/Mantis2Error.h:
+// 67-68), and the colour error and the count of projected points run on over the cameras (the `projected` argument
+// of computeImageError, :55-99; MonteCarlo.cpp:233-241 leaves the second camera as a TODO).  One CTA per rig; every
+// candidate set goes through score_loop once per camera with the integer sums left to accumulate.  With C == 1 and
+// the identity transform this is k_search's arithmetic (tests compare the bytes).
+__global__ void __launch_bounds__(SNT, 1) k_search_rig(SearchArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Shared& s = *reinterpret_cast<Shared*>(smem_raw);
+    __shared__ Tf s_rot_w2c[80], s_rot_c2w[80];
+    __shared__ double s_yaw_err[80];
+    __shared__ int s_yaw_n[80];
+    __shared__ int s_bi;
+    const int tid = threadIdx.x, C = a.C;
+    for (int i = tid; i < a.n_map; i += SNT) {
+        s.map_x[i] = a.map[3 * i]; s.map_y[i] = a.map[3 * i + 1]; s.map_z[i] = a.map[3 * i + 2];
+    }
+    for (int i = a.n_map + tid; i < MAX_MAP; i += SNT) { s.map_x[i] = 0; s.map_y[i] = 0; s.map_z[i] = 0; }
+    for (int i = tid; i < ATAN_N; i += SNT) s.atan_tab[i] = a.atan_tab[i];
+    const bool planar = a.map_planar != 0;
+    for (;;) {
+    __syncthreads();
+    if (tid == 0) s.frame = (int)atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    const int unit = s.frame;
+    if (unit >= a.n) break;
+    mantis_result* out = a.out + unit;
+    mantis_frame_trace* tr = a.trace ? a.trace + unit : nullptr;
+    const FramePose* info = a.info + (size_t)unit * C;
+    const int n_sel = info->n_sel;
+    int flags = 0, nq = 0, ncont = 0, nraw = 0;
+    for (int k = 0; k < C; ++k) {
+        const FrameQuads* fq = a.quads + (size_t)unit * C + k;
+        flags |= fq->flags; nq += fq->n_quads; ncont += fq->n_contours; nraw += fq->n_quads_raw;
+    }
+    if (tid == 0) {
+        out->n_quads = nq; out->n_hyps = n_sel; out->n_particles = 0; out->error = 0; out->min_yaw_diff = 0;
+        for (int k = 0; k < 3; ++k) out->pos[k] = 0;
+        for (int k = 0; k < 4; ++k) out->quat_xyzw[k] = 0;
+        out->status = flags ? MANTIS_FRAME_OVERFLOW : nq == 0 ? MANTIS_FRAME_NO_QUADS : n_sel == 0 ? MANTIS_FRAME_NO_HYPOTHESES : MANTIS_FRAME_OK;
+        if (tr) {
+            tr->n_contours = ncont; tr->n_quads_raw = nraw; tr->n_quads = nq; tr->flags = flags;
+            tr->n_hyps_generated = info->n_hyps_generated; tr->n_hyps_cluster = n_sel; tr->best_rot = -1; tr->pad_ = 0;
+        }
+    }
+    if (flags || nq == 0 || n_sel == 0) continue;
+    const Hyp* hyps = a.hyps + (size_t)unit * C * MANTIS_MAX_HYPS;
+    const short* sel = a.sel + (size_t)unit * C * MANTIS_MAX_HYPS;
+
+    // camera k of the rig becomes the one the scoring loop reads; returns its model (registers)
+    auto set_camera = [&](int k) -> CamK {
+        const int frame = unit * C + k;
+        __syncthreads();
+        CamK cam;
+        const pm::Camera c0 = a.cams[frame];
+        cam.fx = c0.fx; cam.fy = c0.fy; cam.cx = c0.cx; cam.cy = c0.cy;
+        cam.D0 = c0.D[0]; cam.D1 = c0.D[1]; cam.D2 = c0.D[2]; cam.D3 = c0.D[3];
+        cam.has_dist = c0.D[0] != 0 || c0.D[1] != 0 || c0.D[2] != 0 || c0.D[3] != 0;
+        if (tid == 0) {
+            s.img.bgr = a.bgr + (size_t)frame * a.pitch;
+            s.img.mask = a.mask_bits + (size_t)frame * a.H * a.WW;
+            s.img.W = a.W; s.img.H = a.H; s.img.WW = a.WW; s.img.stride = a.stride;
+        }
+        if (tid == 32) {
+            ScoreFrame& f = s.sf;
+            f.fcx = make_double2(cam.fx, cam.cx); f.fcy = make_double2(cam.fy, cam.cy);
+            f.D0 = cam.D0; f.D1 = cam.D1; f.D2 = cam.D2; f.D3 = cam.D3;
+        }
+        if (tid == 64) {
+            const uint8_t* base = a.bgr + (size_t)frame * a.pitch;
+            s.gat.delta = (unsigned)((uintptr_t)base & 3u);
+            s.gat.bgr_al = base - s.gat.delta;
+            s.gat.mask = a.mask_bits + (size_t)frame * a.H * a.WW;   // (global: the planes of C cameras take turns)
+        }
+        __syncthreads();
+        return cam;
+    };
+    // joint WHITE score of the nh base poses in s.cand_w2c -> s.sum / s.cnt (left for err_of)
+    auto score_cands = [&](int nh) {
+        for (int i = tid; i < nh; i += SNT) { s.sum[i] = 0ull; s.cnt[i] = 0; }
+        for (int k = 0; k < C; ++k) {
+            const CamK cam = set_camera(k);
+            if (tid < nh) {
+                Tf wc;
+                pm::tf_mul(s.cand_w2c[tid], a.b2c[unit * C + k], wc);
+                pm::tf_inv(wc, s.cand_c2w[tid]);
+            }
+            __syncthreads();
+            score_loop_call(s, a, nh, (planar ? 2 : 0) | (cam.has_dist ? 1 : 0));
+        }
+        __syncthreads();
+    };
+    auto err_of = [&](int i) { return s.cnt[i] > 0 ? (double)s.sum[i] / ((double)s.cnt[i] * a.projection_bias) : DBLMAX; };
+
+    // (6) evaluateHypotheses on the kept cluster, 96 at a time, (7) best 1: stable descending sort, last element
+    if (tid == 0) { s.best.error = DBLMAX; s_bi = -1; }
+    for (int base = 0; base < n_sel; base += 96) {
+        const int nh = min(96, n_sel - base);
+        __syncthreads();
+        if (tid < nh) s.cand_w2c[tid] = hyps[sel[base + tid]].w2c;
+        __syncthreads();
+        score_cands(nh);
+        if (tid == 0)
+            for (int i = 0; i < nh; ++i) {
+                const double e = err_of(i);
+                if (s_bi < 0 || e <= s.best.error) { s.best.error = e; s.best.w2c = s.cand_w2c[i]; s_bi = base + i; }
+            }
+    }
+    __syncthreads();
+    if (tid == 0 && tr) tr->first_best_error = s.best.error;
+
+    // (8) optimizeHypothesisWithParticleFilter on the base pose
+    for (int it = 0; it < a.iterations; ++it) {
+        const int nh = a.particles;
+        __syncthreads();
+        if (tid < nh) pm::tf_mul(s.best.w2c, a.rand_tf[it * a.particles + tid], s.cand_w2c[tid]);
+        __syncthreads();
+        score_cands(nh);
+        if (tid < 32) {
+            double e = DBLMAX;
+            int bp = 0x7fffffff;
+            for (int p2 = tid; p2 < nh; p2 += 32) {
+                const double ep = err_of(p2);
+                if (ep < e) { e = ep; bp = p2; }
+            }
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) {
+                const double eo = __shfl_xor_sync(0xffffffffu, e, d);
+                const int po = __shfl_xor_sync(0xffffffffu, bp, d);
+                if (eo < e || (eo == e && po < bp)) { e = eo; bp = po; }
+            }
+            if (e < s.best.error) {
+                __syncwarp();
+                if (tid < 12) ((double*)&s.best.w2c)[tid] = ((const double*)&s.cand_w2c[bp])[tid];
+                else if (tid == 24) s.best.error = e;
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0 && tr) {
+        tr->optimized_error = s.best.error;
+        for (int k = 0; k < 9; ++k) tr->optimized_w2c[k] = s.best.w2c.R[k];
+        for (int k = 0; k < 3; ++k) tr->optimized_w2c[9 + k] = s.best.w2c.t[k];
+    }
+
+    // (9) the cell shifts of the base origin, (10) evaluate, (11) best 20
+    const int ns = a.n_shift, keep = ns < 20 ? ns : 20;
+    __syncthreads();
+    if (tid < ns) {
+        Tf w = s.best.w2c;
+        w.t[0] += a.shifts[2 * tid];
+        w.t[1] += a.shifts[2 * tid + 1];
+        w.t[2] += 0;
+        s.cand_w2c[tid] = w;
+    }
+    __syncthreads();
+    score_cands(ns);
+    for (int i = tid; i < ns; i += SNT) s.err[i] = err_of(i);
+    __syncthreads();
+    if (tr)
+        for (int i = tid; i < ns && i < 81; i += SNT) tr->shift_err[i] = s.err[i];
+    if (tid < ns) {
+        if (ns <= 20) {
+            s.top20[tid] = (short)tid;
+        } else {
+            int pos = 0;
+            const double e = s.err[tid];
+            for (int j = 0; j < ns; ++j) pos += (s.err[j] > e) || (s.err[j] == e && j < tid);
+            if (pos >= ns - keep) s.top20[pos - (ns - keep)] = (short)tid;
+        }
+    }
+    __syncthreads();
+
+    // (12) determineBestYaw on the original images, joint over the cameras
+    if (tid < keep) {
+        Tf w = s.cand_w2c[s.top20[tid]];
+        for (int r = 0; r < 4; ++r) {
+            if (r > 0) { Tf t2; pm::tf_mul(a.rotz, w, t2); w = t2; }
+            s_rot_w2c[r * keep + tid] = w;
+        }
+    }
+    const int ng = a.n_green, nrot = 4 * keep;
+    if (tid < nrot) { s_yaw_err[tid] = 0; s_yaw_n[tid] = 0; }
+    for (int k = 0; k < C; ++k) {
+        const CamK cam = set_camera(k);
+        const Img& im = s.img;
+        if (tid < nrot) {
+            Tf wc;
+            pm::tf_mul(s_rot_w2c[tid], a.b2c[unit * C + k], wc);
+            pm::tf_inv(wc, s_rot_c2w[tid]);
+        }
+        __syncthreads();
+        for (int item = tid; item < nrot * ng; item += SNT) {
+            const int h = item / ng, gi = item - h * ng, mi = a.n_green_off + gi;
+            double u, v;
+            const bool ok = project(load_pose(s_rot_c2w[h]), cam, s.map_x[mi], s.map_y[mi], s.map_z[mi], planar, s.atan_tab, im.W, im.H, u, v);
+            const int slot = h * 40 + gi;
+            unsigned int acc = 0;
+            if (ok)
+                for (int dx = -5; dx < 5; ++dx)
+                    for (int dy = -5; dy < 5; ++dy)
+                        acc += (unsigned)pixel_err(im, __double2int_rn(u + (double)dx), __double2int_rn(v + (double)dy), false, 50, 255, 85);
+            s.green_acc[slot] = acc;
+            s.green_xy[slot] = ok ? 0 : -1;
+        }
+        __syncthreads();
+        if (tid < nrot)
+            for (int gi = 0; gi < ng; ++gi)
+                if (s.green_xy[tid * 40 + gi] >= 0) { s_yaw_err[tid] += (double)s.green_acc[tid * 40 + gi] / 100.0; ++s_yaw_n[tid]; }
+    }
+    __syncthreads();
+    if (tid < nrot) s.hyp_err[tid] = s_yaw_n[tid] > 0 ? s_yaw_err[tid] / ((double)s_yaw_n[tid] * a.color_bias) : DBLMAX;
+    __syncthreads();
+    if (tid == 0) {
+        double yaw[4], best_error = DBLMAX;
+        int best = -1;
+        for (int r = 0; r < 4; ++r) {
+            double total = 0;
+            int success = 0;
+            for (int k = 0; k < keep; ++k) {
+                double e = s.hyp_err[r * keep + k];
+                if (fabs(e - DBLMAX) > 0.001) { success++; total += e; }
+            }
+            yaw[r] = success ? total / (double)success : DBLMAX;
+            if (yaw[r] < best_error) { best_error = yaw[r]; best = r; }
+        }
+        double min1 = DBLMAX, min2 = DBLMAX;
+        for (int r = 0; r < 4; ++r) {
+            double diff = yaw[r] - best_error;
+            if (diff < min1) { min2 = min1; min1 = diff; }
+            else if (diff < min2) min2 = diff;
+        }
+        out->min_yaw_diff = min2;
+        out->n_particles = n_sel + 1 + a.iterations * a.particles + ns + nrot;
+        if (tr) { for (int r = 0; r < 4; ++r) tr->yaw_err[r] = yaw[r]; tr->best_rot = best; }
+        if (best < 0) {
+            out->status = MANTIS_FRAME_YAW_FAILED;
+        } else {
+            const Tf& w = s_rot_w2c[best * keep + keep - 1];  // hyps.back()
+            for (int k = 0; k < 3; ++k) out->pos[k] = w.t[k];
+            pm::mat_to_quat(w.R, out->quat_xyzw);
+            out->error = s.hyp_err[best * keep + keep - 1];
+        }
+    }
+    }  // rig loop
+}
+
 }  // namespace
 
 static int launch_search_impl(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n,
                               int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
                               const short* d_sel, const FramePose* d_info, mantis_result* d_out, mantis_frame_trace* d_trace,
-                              const double* d_ext_w2c, int ext_n, double* d_ext_scores)
+                              const double* d_ext_w2c, int ext_n, double* d_ext_scores, int rig_cams = 0,
+                              const Tf* d_b2c = nullptr)
 {
     if (c->n_map <= 0 || c->n_map > MAX_MAP || c->n_green > 40 || c->n_shift > 96 || c->cfg.particles > 96) {
         snprintf(c->err, sizeof(c->err), "map / search sizes exceed the kernel's limits (map %d, green %d)", c->n_map, c->n_green);
@@ -714,6 +978,7 @@ static int launch_search_impl(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch,
     a.out = d_out; a.trace = d_trace;
     a.dbg = (long long*)c->dbg_clocks;
     a.ext_w2c = d_ext_w2c; a.ext_n = ext_n; a.ext_scores = d_ext_scores;
+    a.C = rig_cams > 0 ? rig_cams : 1; a.b2c = d_b2c;
     // persistent CTAs (one per SM); frames come from a ticket counter
     const int grid = n < c->sm_count ? n : c->sm_count;
     int rc = ctx_reserve(c, c->search_ticket, sizeof(unsigned));
@@ -722,6 +987,14 @@ static int launch_search_impl(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch,
     a.n = n;
     MCHECK(c, cudaMemsetAsync(a.ticket, 0, sizeof(unsigned), c->stream));
     size_t smem = sizeof(Shared);
+    if (rig_cams > 0) {   // n = rigs; the mask planes of the rig's cameras are read from global memory
+        a.mask_in_smem = 0;
+        MCHECK(c, cudaFuncSetAttribute(k_search_rig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_search_rig<<<grid, SNT, smem, c->stream>>>(a);
+        c->launches++;
+        MCHECK(c, cudaGetLastError());
+        return MANTIS_OK;
+    }
     {
         cudaFuncAttributes fa;
         MCHECK(c, cudaFuncGetAttributes(&fa, k_search));
@@ -750,4 +1023,14 @@ int launch_score(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, 
 {
     return launch_search_impl(c, d_bgr, pitch, stride, d_mask_bits, n, w, h, d_cams, nullptr, nullptr, nullptr, nullptr, nullptr,
                               nullptr, d_w2c, n_hyps, d_scores);
+}
+
+// Rigs: n_rigs units of rig_cams consecutive frames; d_hyps / d_sel / d_info as launch_pose(..., rig_cams, ...) left them.
+int launch_search_rig(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch, int stride, const uint32_t* d_mask_bits, int n_rigs,
+                      int rig_cams, int w, int h, const pm::Camera* d_cams, const FrameQuads* d_quads, const Hyp* d_hyps,
+                      const short* d_sel, const FramePose* d_info, const Tf* d_b2c, mantis_result* d_out,
+                      mantis_frame_trace* d_trace)
+{
+    return launch_search_impl(c, d_bgr, pitch, stride, d_mask_bits, n_rigs, w, h, d_cams, d_quads, d_hyps, d_sel, d_info, d_out,
+                              d_trace, nullptr, 0, nullptr, rig_cams, d_b2c);
 }

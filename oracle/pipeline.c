@@ -430,44 +430,58 @@ static int project(const mo_hyp* hyp, const double* p, const float* K, const dou
     return (px[0] < w && px[1] < h && px[0] >= 0 && px[1] > 0); /* inFrame, HypothesisEvaluation.h:388 */
 }
 
-/* evaluateHypothesis (fast path) on the edge-masked image, HypothesisEvaluation.h:71-158 */
-double mo_score_white(const mo_hyp* hyp, const uint8_t* bgr, const uint8_t* mask, int w, int h, int stride,
-                      const float* K, const double* D, const mo_map* map, double bias)
+/* evaluateHypothesis (fast path) on the edge-masked image, HypothesisEvaluation.h:71-158: colour error and number of
+ * projected points, ADDED to *err / *n (computeImageError's `projected` is a running count over the cameras of a rig,
+ * include/legacy/mantis2/Mantis2Error.h:32-53,55-99) */
+static void accum_white(const mo_hyp* hyp, const uint8_t* bgr, const uint8_t* mask, int w, int h, int stride, const float* K,
+                        const double* D, const mo_map* map, double* err, int* n)
 {
     static const int WHITE[3] = {255, 255, 255};
     const double* sets[3] = {map->white, map->red, map->green};
     const int counts[3] = {map->n_white, map->n_red, map->n_green};
-    double err = 0;
-    int n = 0;
     for (int s = 0; s < 3; ++s)
         for (int i = 0; i < counts[s]; ++i) {
             double px[2];
             if (!project(hyp, sets[s] + 3 * i, K, D, w, h, px)) continue;
-            n++;
-            err += (double)pixel_err(bgr, mask, w, h, stride, cv_round(px[0]), cv_round(px[1]), WHITE);
+            (*n)++;
+            *err += (double)pixel_err(bgr, mask, w, h, stride, cv_round(px[0]), cv_round(px[1]), WHITE);
         }
+}
+
+double mo_score_white(const mo_hyp* hyp, const uint8_t* bgr, const uint8_t* mask, int w, int h, int stride,
+                      const float* K, const double* D, const mo_map* map, double bias)
+{
+    double err = 0;
+    int n = 0;
+    accum_white(hyp, bgr, mask, w, h, stride, K, D, map, &err, &n);
     if (n <= 0) return DBL_MAX;
     return err / ((double)n * bias);
 }
 
 /* evaluateHypothesisCOLOR (slow path, GREEN_ONLY) on the original image, :89-105,160-266 */
-double mo_score_green(const mo_hyp* hyp, const uint8_t* bgr, int w, int h, int stride, const float* K,
-                      const double* D, const mo_map* map, double bias)
+static void accum_green(const mo_hyp* hyp, const uint8_t* bgr, int w, int h, int stride, const float* K, const double* D,
+                        const mo_map* map, double* err, int* n)
 {
     static const int GREEN[3] = {50, 255, 85};
-    double err = 0;
-    int n = 0;
     for (int i = 0; i < map->n_green; ++i) {
         double px[2];
         if (!project(hyp, map->green + 3 * i, K, D, w, h, px)) continue;
-        n++;
+        (*n)++;
         double e = 0;
         for (double x = -5.0; x < 5.0; x += 1)
             for (double y = -5.0; y < 5.0; y += 1)
                 e += (double)pixel_err(bgr, NULL, w, h, stride, cv_round(px[0] + x), cv_round(px[1] + y), GREEN);
         e /= 100.0;
-        err += e;
+        *err += e;
     }
+}
+
+double mo_score_green(const mo_hyp* hyp, const uint8_t* bgr, int w, int h, int stride, const float* K,
+                      const double* D, const mo_map* map, double bias)
+{
+    double err = 0;
+    int n = 0;
+    accum_green(hyp, bgr, w, h, stride, K, D, map, &err, &n);
     if (n <= 0) return DBL_MAX;
     return err / ((double)n * bias);
 }
@@ -488,21 +502,63 @@ static int best_n(mo_hyp* hyps, int count, int n)
     return n;
 }
 
+/* One camera of the rig a hypothesis is scored on.  A hypothesis is the pose of the BASE in the world; camera k sees
+ * it as W2C_k = W2B * b2c_k (Mantis2Error.h:67-68: new_hyp.setW2C(hyp.getW2C() * b2c); MantisRequest.h:14-26).
+ * A single camera without extrinsics (mantis3's quadDetection) is the case n_cams == 1, has_b2c == 0. */
 typedef struct {
     const uint8_t* bgr;
     const uint8_t* mask;
-    int w, h, stride;
     const float* K;
     const double* D;
+    mo_tf b2c;
+    int has_b2c;
+} eval_cam;
+
+typedef struct {
+    int n_cams;
+    eval_cam cam[MO_MAX_RIG];
+    int w, h, stride;
     const mo_map* map;
     const mo_params* prm;
     long scored;
 } eval_ctx;
 
+static void camera_hyp(const eval_cam* c, const mo_hyp* hyp, mo_hyp* out)
+{
+    if (!c->has_b2c) { *out = *hyp; return; }
+    mo_tf w2c;
+    tf_mul(&hyp->w2c, &c->b2c, &w2c);
+    *out = *hyp;
+    mo_hyp_set_w2c(out, &w2c);
+}
+
+/* joint score: summed colour error over the cameras / (summed projected points * bias) */
 static double eval_white(eval_ctx* e, const mo_hyp* hyp)
 {
     e->scored++;
-    return mo_score_white(hyp, e->bgr, e->mask, e->w, e->h, e->stride, e->K, e->D, e->map, e->prm->projection_bias);
+    double err = 0;
+    int n = 0;
+    for (int k = 0; k < e->n_cams; ++k) {
+        mo_hyp ch;
+        camera_hyp(&e->cam[k], hyp, &ch);
+        accum_white(&ch, e->cam[k].bgr, e->cam[k].mask, e->w, e->h, e->stride, e->cam[k].K, e->cam[k].D, e->map, &err, &n);
+    }
+    if (n <= 0) return DBL_MAX;
+    return err / ((double)n * e->prm->projection_bias);
+}
+
+static double eval_green(eval_ctx* e, const mo_hyp* hyp)
+{
+    e->scored++;
+    double err = 0;
+    int n = 0;
+    for (int k = 0; k < e->n_cams; ++k) {
+        mo_hyp ch;
+        camera_hyp(&e->cam[k], hyp, &ch);
+        accum_green(&ch, e->cam[k].bgr, e->w, e->h, e->stride, e->cam[k].K, e->cam[k].D, e->map, &err, &n);
+    }
+    if (n <= 0) return DBL_MAX;
+    return err / ((double)n * e->prm->color_projection_bias);
 }
 
 /* generateRandomHypothesis, PoseAdjustment.h:13-23 (argument lists evaluated right to left) */
@@ -539,34 +595,83 @@ static void optimize_hypothesis(eval_ctx* e, const mo_hyp* in, uint64_t* rng, mo
     *out = best;
 }
 
-/* ------------------------------------------------------------------ the frame */
-int mo_localize(const uint8_t* bgr, int w, int h, int stride, const float* K, const double* D,
-                const mo_params* prm, const mo_map* map, mo_trace* tr, uint8_t* mask_out)
+/* ------------------------------------------------------------------ the frame / the rig */
+/* quadDetection() (src/mantis3.cpp:68-135) for n_cams cameras of one rig.  n_cams == 1 without extrinsics is the
+ * reference's callback itself.  With extrinsics (cam_to_base: x y z qx qy qz qw per camera, the b2c of
+ * MantisRequest.h:14-26) every camera contributes its quads' hypotheses, moved to the BASE frame
+ * (W2B = W2C_k * b2c_k^-1), the rotation clustering runs on the pooled set, and every score from step (6) on is the
+ * joint one of eval_white / eval_green: the multi-camera refinement the reference states as its intent
+ * (MonteCarlo.cpp:233-241 "w2c2 ... TODO", Mantis2Error.h:55-99) and never finished.  tr's quad arrays hold the quads
+ * of all cameras in camera order; the pose is the base's. */
+static int localize_impl(int n_cams, const uint8_t* const* bgrs, int w, int h, int stride, const float* Ks, const double* Ds,
+                         const double* cam_to_base, const mo_params* prm, const mo_map* map, mo_trace* tr, uint8_t* mask_out)
 {
     memset(tr, 0, sizeof(*tr));
+    if (n_cams < 1 || n_cams > MO_MAX_RIG) return -1;
     size_t n = (size_t)w * h;
     uint8_t* canny = malloc(n);
     uint8_t* morph = malloc(n);
-    uint8_t* mask = malloc(n);
+    uint8_t* masks = malloc(n * (size_t)n_cams);
     mo_hyp* hyps = malloc(sizeof(mo_hyp) * (MO_MAX_HYPS + 4));
     mo_hyp* sel = malloc(sizeof(mo_hyp) * (MO_MAX_HYPS + 4));
     int* members = malloc(sizeof(int) * (MO_MAX_HYPS + 4));
+    mo_trace* one = n_cams > 1 ? malloc(sizeof(mo_trace)) : tr;
     int status = MO_OK;
+    eval_ctx e;
+    memset(&e, 0, sizeof(e));
+    e.n_cams = n_cams; e.w = w; e.h = h; e.stride = stride; e.map = map; e.prm = prm;
 
-    /* (1) detectQuadrilaterals, src/mantis3.cpp:79 */
-    mo_edge_stage(bgr, w, h, stride, prm->canny_hysteresis, canny, morph);
-    int nq = mo_detect_quads(morph, w, h, prm, tr);
-    if (nq == 0) { status = MO_NO_QUADS; goto done; }
-
-    /* (2) undistortAndNormalizeQuadTestPoints + (3) generateHypotheses, :87 */
-    int nh = 0;
-    for (int i = 0; i < nq; ++i) {
-        mo_fisheye_undistort(tr->quad_test_px[i], 4, K, D, tr->quad_test_norm[i]);
-        mo_hyp four[4];
-        int pass = central_hypotheses(tr->quad_test_norm[i], prm, four, &tr->quad_img_err[i]);
-        tr->quad_pass[i] = pass;
-        if (pass) { memcpy(hyps + nh, four, sizeof(four)); nh += 4; }
+    int nq_total = 0, nh = 0;
+    for (int k = 0; k < n_cams; ++k) {
+        const float* K = Ks + 9 * k;
+        const double* D = Ds + 4 * k;
+        eval_cam* c = &e.cam[k];
+        c->bgr = bgrs[k]; c->K = K; c->D = D; c->mask = masks + n * (size_t)k;
+        c->has_b2c = cam_to_base != NULL;
+        mo_tf b2c_inv;
+        if (c->has_b2c) {
+            const double* q = cam_to_base + 7 * k;
+            quat_to_mat(q + 3, c->b2c.R);
+            memcpy(c->b2c.t, q, sizeof(double) * 3);
+            tf_inv(&c->b2c, &b2c_inv);
+        }
+        /* (1) detectQuadrilaterals, src/mantis3.cpp:79 */
+        mo_edge_stage(bgrs[k], w, h, stride, prm->canny_hysteresis, canny, morph);
+        /* (5) cleanImageByEdge, :102 (needs this camera's Canny map; used from step (6) on) */
+        mo_clean_mask(canny, w, h, masks + n * (size_t)k);
+        if (n_cams > 1) memset(one, 0, sizeof(*one));
+        int nq = mo_detect_quads(morph, w, h, prm, one);
+        /* (2) undistortAndNormalizeQuadTestPoints + (3) generateHypotheses, :87 */
+        for (int i = 0; i < nq; ++i) {
+            mo_fisheye_undistort(one->quad_test_px[i], 4, K, D, one->quad_test_norm[i]);
+            mo_hyp four[4];
+            int pass = central_hypotheses(one->quad_test_norm[i], prm, four, &one->quad_img_err[i]);
+            one->quad_pass[i] = pass;
+            if (!pass) continue;
+            if (c->has_b2c)
+                for (int j = 0; j < 4; ++j) {   /* camera pose -> base pose */
+                    mo_tf w2b;
+                    tf_mul(&four[j].w2c, &b2c_inv, &w2b);
+                    mo_hyp_set_w2c(&four[j], &w2b);
+                }
+            if (nh + 4 <= MO_MAX_HYPS) { memcpy(hyps + nh, four, sizeof(four)); nh += 4; }
+        }
+        if (n_cams > 1) {   /* append this camera's quads to the rig's trace */
+            tr->n_contours += one->n_contours;
+            tr->n_quads_raw += one->n_quads_raw;
+            for (int i = 0; i < nq && nq_total + i < MO_MAX_QUADS; ++i) {
+                memcpy(tr->quad_corners[nq_total + i], one->quad_corners[i], sizeof(one->quad_corners[i]));
+                memcpy(tr->quad_test_px[nq_total + i], one->quad_test_px[i], sizeof(one->quad_test_px[i]));
+                memcpy(tr->quad_test_norm[nq_total + i], one->quad_test_norm[i], sizeof(one->quad_test_norm[i]));
+                tr->quad_pass[nq_total + i] = one->quad_pass[i];
+                tr->quad_img_err[nq_total + i] = one->quad_img_err[i];
+            }
+        }
+        nq_total += nq;
     }
+    tr->n_quads = nq_total;
+    if (mask_out) memcpy(mask_out, masks, n);
+    if (nq_total == 0) { status = MO_NO_QUADS; goto done; }
     tr->n_hyps_generated = nh;
 
     /* (4) cluster by angle, keep the largest cluster, :90-92 */
@@ -574,11 +679,6 @@ int mo_localize(const uint8_t* bgr, int w, int h, int stride, const float* K, co
     for (int k = 0; k < nc; ++k) sel[k] = hyps[members[k]];
     tr->n_hyps_cluster = nc;
     if (nc == 0) { status = MO_NO_HYPOTHESES; goto done; }
-
-    /* (5) cleanImageByEdge, :102 */
-    mo_clean_mask(canny, w, h, mask);
-    if (mask_out) memcpy(mask_out, mask, n);
-    eval_ctx e = {bgr, mask, w, h, stride, K, D, map, prm, 0};
 
     /* (6) evaluateHypotheses (7) best 1, :107-110 */
     for (int k = 0; k < nc; ++k) sel[k].error = eval_white(&e, &sel[k]);
@@ -629,8 +729,7 @@ int mo_localize(const uint8_t* bgr, int w, int h, int stride, const float* K, co
             double total = 0;
             int success = 0;
             for (int j = 0; j < ns; ++j) {
-                e.scored++;
-                rots[r][j].error = mo_score_green(&rots[r][j], bgr, w, h, stride, K, D, map, prm->color_projection_bias);
+                rots[r][j].error = eval_green(&e, &rots[r][j]);
                 if (fabs(rots[r][j].error - DBL_MAX) > 0.001) { success++; total += rots[r][j].error; }
             }
             tr->yaw_err[r] = success ? total / (double)success : DBL_MAX;
@@ -656,6 +755,19 @@ int mo_localize(const uint8_t* bgr, int w, int h, int stride, const float* K, co
     tr->n_scored = e.scored;
 done:
     tr->status = status;
-    free(canny); free(morph); free(mask); free(hyps); free(sel); free(members);
+    if (n_cams > 1) free(one);
+    free(canny); free(morph); free(masks); free(hyps); free(sel); free(members);
     return status;
+}
+
+int mo_localize(const uint8_t* bgr, int w, int h, int stride, const float* K, const double* D,
+                const mo_params* prm, const mo_map* map, mo_trace* tr, uint8_t* mask_out)
+{
+    return localize_impl(1, &bgr, w, h, stride, K, D, NULL, prm, map, tr, mask_out);
+}
+
+int mo_localize_rig(const uint8_t* const* bgr, int n_cams, int w, int h, int stride, const float* K, const double* D,
+                    const double* cam_to_base, const mo_params* prm, const mo_map* map, mo_trace* tr)
+{
+    return localize_impl(n_cams, bgr, w, h, stride, K, D, cam_to_base, prm, map, tr, NULL);
 }

@@ -12,6 +12,7 @@ extern "C" {
 
 #define MO_MAX_QUADS 1024
 #define MO_MAX_HYPS (4 * MO_MAX_QUADS)
+#define MO_MAX_RIG 8 /* cameras per rig */
 
 /* tf::Transform: basis (row-major) + origin */
 typedef struct mo_tf { double R[9]; double t[3]; } mo_tf;
@@ -68,6 +69,11 @@ typedef struct mo_trace {
  * mask_out (optional, w*h) receives cleanImageByEdge's mask {0,255}. */
 int mo_localize(const uint8_t* bgr, int w, int h, int stride, const float* K, const double* D,
                 const mo_params* prm, const mo_map* map, mo_trace* tr, uint8_t* mask_out);
+
+/* A rig of n_cams cameras (one image, K (9), D (4) and camera->base transform (x y z qx qy qz qw) each) localized
+ * jointly: see localize_impl in pipeline.c.  The pose in tr is the BASE's. */
+int mo_localize_rig(const uint8_t* const* bgr, int n_cams, int w, int h, int stride, const float* K, const double* D,
+                    const double* cam_to_base, const mo_params* prm, const mo_map* map, mo_trace* tr);
 
 /* pieces exposed for unit checks */
 void mo_clean_mask(const uint8_t* canny, int w, int h, uint8_t* mask);

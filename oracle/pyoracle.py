@@ -274,6 +274,22 @@ def localize(bgr, K, D, params=None, maps=None, want_mask=False):
     return tr, mask
 
 
+def localize_rig(frames, Ks, Ds, cam_to_base, params=None, maps=None):
+    """Joint localization of one rig: frames [C,H,W,3], Ks [C,3,3], Ds [C,4], cam_to_base [C,7] (x y z qx qy qz qw of
+    each camera in the base frame; None = a single camera without extrinsics).  Returns the Trace (base pose)."""
+    frames = np.ascontiguousarray(frames, np.uint8)
+    C, h, w, _ = frames.shape
+    Ks = np.ascontiguousarray(Ks, np.float32).reshape(C, 9)
+    Ds = np.ascontiguousarray(Ds, np.float64).reshape(C, 4)
+    ptrs = (ctypes.c_void_p * C)(*[frames[k].ctypes.data for k in range(C)])
+    b2c = None if cam_to_base is None else np.ascontiguousarray(cam_to_base, np.float64).reshape(C, 7)
+    prm = params if params is not None else default_params()
+    tr = Trace()
+    lib().mo_localize_rig(ptrs, C, w, h, 3 * w, _dp(Ks), _dp(Ds), _dp(b2c) if b2c is not None else None, ctypes.byref(prm),
+                          ctypes.byref(_map_struct(maps)), ctypes.byref(tr))
+    return tr
+
+
 def score_white(w2c12, bgr, K, D, maps=None, bias=1.1):
     """evaluateHypothesisWithImageWHITE on cleanImageByEdge's image (HypothesisEvaluation.h:107-158, 319-386) for the
     hypothesis whose W2C is w2c12 (R row-major + t)."""

@@ -36,3 +36,36 @@ def random_pose(rng):
 def poses(n, seed=SEED):
     rng = np.random.default_rng(seed)
     return [random_pose(rng) for _ in range(n)]
+
+
+def quat_xyzw(R):
+    """Rotation matrix -> unit quaternion (x, y, z, w), w >= 0."""
+    w = np.sqrt(max(0.0, 1 + R[0, 0] + R[1, 1] + R[2, 2])) / 2
+    if w > 1e-6:
+        q = np.array([(R[2, 1] - R[1, 2]) / (4 * w), (R[0, 2] - R[2, 0]) / (4 * w), (R[1, 0] - R[0, 1]) / (4 * w), w])
+    else:
+        i = int(np.argmax(np.diag(R)))
+        j, k = (i + 1) % 3, (i + 2) % 3
+        s = np.sqrt(max(0.0, 1 + R[i, i] - R[j, j] - R[k, k])) * 2
+        q = np.zeros(4)
+        q[i] = s / 4
+        q[j] = (R[j, i] + R[i, j]) / s
+        q[k] = (R[k, i] + R[i, k]) / s
+        q[3] = (R[k, j] - R[j, k]) / s
+    return q / np.linalg.norm(q)
+
+
+def rig_extrinsics():
+    """four cameras on the base -- straight down, 30 degrees fore, 30 degrees aft, 30 degrees to the
+    side -- each 5 cm off the base origin.  Returns [(R_b2c, t_b2c)] = the pose of each camera in the base frame (the
+    base frame is itself a down-looking camera frame: x right, y back, z down)."""
+    a = np.deg2rad(30)
+    out = [(np.eye(3), np.array([0.0, 0.0, 0.0])),
+           (rpy_matrix(a, 0, 0), np.array([0.0, -0.05, 0.0])),
+           (rpy_matrix(-a, 0, 0), np.array([0.0, 0.05, 0.0])),
+           (rpy_matrix(0, a, 0), np.array([0.05, 0.0, 0.0]))]
+    return out
+
+
+def rig_cam_to_base():
+    return np.array([np.concatenate([t, quat_xyzw(R)]) for R, t in rig_extrinsics()])

