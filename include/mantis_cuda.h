@@ -292,6 +292,20 @@ int mantis_localize_batch(mantis_ctx* ctx, const mantis_frame* frames, int n, ma
                           mantis_frame_trace* trace, int mem);
 
 /*
+ * Asynchronous form of mantis_localize_batch: returns as soon as the whole batch (all its chunks) is queued on the
+ * context's streams, so one host thread can keep several devices busy, or prepare the next batch meanwhile.
+ * frames' pixels, out and trace must stay valid -- and the context idle otherwise -- until mantis_wait(ctx) has
+ * returned MANTIS_OK; only then are out / trace filled.  With pageable (non-pinned) out / trace the runtime makes
+ * the result copies synchronous and the call degrades gracefully towards the blocking one.  Errors detected while
+ * queueing are returned at once (the streams are drained first); mantis_wait reports CUDA errors raised later.
+ * Not available while per-stage profiling is on.  (The reference's callback is synchronous: src/mantis3.cpp:68-135
+ * runs on the ros::spin() thread, :155.)
+ */
+int mantis_localize_batch_async(mantis_ctx* ctx, const mantis_frame* frames, int n, mantis_result* out,
+                                mantis_frame_trace* trace, int mem);
+int mantis_wait(mantis_ctx* ctx);
+
+/*
  * Rigs: joint multi-camera localization (BASELINE.json configs[2]).  frames holds n_rigs x cams_per_rig records, the
  * cameras of a rig next to each other, each with its cam_to_base -- the per-camera base->camera transform of the
  * reference's requests (tf::StampedTransform b2c, include/legacy/mantis/MantisRequest.h:14-26).  Every camera runs

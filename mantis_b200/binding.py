@@ -187,6 +187,8 @@ def load_library():
                                                 c.c_int, c.c_int]
     lib.mantis_set_map.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int]
     lib.mantis_localize_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_localize_batch_async.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
+    lib.mantis_wait.argtypes = [c.c_void_p]
     lib.mantis_localize_rig_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_void_p, c.c_void_p, c.c_int]
     lib.mantis_render_grid_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int, c.c_void_p,
                                              c.c_void_p, c.c_double, c.c_int, c.c_float, c.c_uint32, c.c_void_p,
@@ -504,6 +506,16 @@ class Context:
                                              ctypes.addressof(tr) if want_trace else None, mem)
         self._check(rc, "mantis_localize_batch")
         return out, tr
+
+    def localize_frames_async(self, frames, mem, out, trace=None):
+        """mantis_localize_batch_async: queue the batch; `out` (Result array, ideally in pinned memory) is filled once
+        wait() has returned.  Keep `frames` and `out` alive until then."""
+        rc = self._lib.mantis_localize_batch_async(self._h, ctypes.addressof(frames), len(frames), ctypes.addressof(out),
+                                                   ctypes.addressof(trace) if trace is not None else None, mem)
+        self._check(rc, "mantis_localize_batch_async")
+
+    def wait(self):
+        self._check(self._lib.mantis_wait(self._h), "mantis_wait")
 
     # -- synthetic frame source (stands in for GridRenderer.cpp:292-353) --
     def render_grid_device(self, poses, w, h, K, D, d_out, line_width=0.04, floor_level=30, noise_sigma=0.0, seed=0):

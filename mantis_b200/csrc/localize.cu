@@ -109,7 +109,7 @@ extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int
 // are rigs of rig_cams cameras localized jointly through their cam_to_base (mantis_localize_rig_batch); out / trace then
 // hold one record per rig.
 static int localize_impl(mantis_ctx* c, const mantis_frame* frames, int n, mantis_result* out, mantis_frame_trace* trace,
-                         int mem, int rig_cams)
+                         int mem, int rig_cams, bool async = false)
 {
     if (!c || n < 0 || (n > 0 && (!frames || !out)) || (mem != MANTIS_MEM_HOST && mem != MANTIS_MEM_DEVICE))
         return MANTIS_ERR_INVALID;
@@ -146,7 +146,7 @@ static int localize_impl(mantis_ctx* c, const mantis_frame* frames, int n, manti
     // frames for 1 / 2 / 3 lanes), so the default is 1.  Per-stage profiling always uses the single-lane path.
     static const int lanes_env = []() { const char* e = getenv("MANTIS_LANES"); return e ? atoi(e) : 1; }();
     const int L = lanes_env > mantis_ctx::MAX_LANES ? mantis_ctx::MAX_LANES : lanes_env;
-    if (!rig && mem == MANTIS_MEM_DEVICE && !c->is_lane && !c->profiling && L >= 2 && n >= 512 * L) {
+    if (!rig && !async && mem == MANTIS_MEM_DEVICE && !c->is_lane && !c->profiling && L >= 2 && n >= 512 * L) {
         for (int i = 0; i < L; ++i)
             if (!c->lane[i]) {
                 int rc0 = mantis_create(&c->cfg, c->device, &c->lane[i]);
@@ -321,8 +321,13 @@ static int localize_impl(mantis_ctx* c, const mantis_frame* frames, int n, manti
             MCHECK(c, cudaMemcpyAsync(trace + f0 / UC, c->traces.p, sizeof(mantis_frame_trace) * (size_t)(nc / UC),
                                       cudaMemcpyDeviceToHost, c->stream));
         prof_mark(c, 7);
-        MCHECK(c, cudaStreamSynchronize(c->stream));
-        prof_collect(c, 0, MANTIS_N_STAGES);
+        // Everything above is ordered by the streams (scratch is reused chunk after chunk on c->stream, the staging
+        // buffers through events), and the runtime has staged the pageable host sources (camera tables) before each
+        // cudaMemcpyAsync returned: the host only has to wait when the caller wants the results now.
+        if (!async) {
+            MCHECK(c, cudaStreamSynchronize(c->stream));
+            prof_collect(c, 0, MANTIS_N_STAGES);
+        }
     }
     return MANTIS_OK;
     };
@@ -346,4 +351,22 @@ extern "C" int mantis_localize_rig_batch(mantis_ctx* c, const mantis_frame* fram
     if (cams_per_rig < 1 || cams_per_rig > MANTIS_MAX_RIG_CAMERAS || n_rigs < 0 || (long long)n_rigs * cams_per_rig > 0x7fffffffLL)
         return MANTIS_ERR_INVALID;
     return localize_impl(c, frames, n_rigs * cams_per_rig, out, trace, mem, cams_per_rig);
+}
+
+// Asynchronous form: returns once the work is queued on the context's streams.  out / trace (and host frames) must
+// stay valid, and the context must not be used for anything else, until mantis_wait() returns.
+extern "C" int mantis_localize_batch_async(mantis_ctx* c, const mantis_frame* frames, int n, mantis_result* out,
+                                           mantis_frame_trace* trace, int mem)
+{
+    if (c && c->profiling) return MANTIS_ERR_INVALID;   // per-stage timing needs the synchronous call
+    return localize_impl(c, frames, n, out, trace, mem, 0, true);
+}
+
+extern "C" int mantis_wait(mantis_ctx* c)
+{
+    if (!c) return MANTIS_ERR_INVALID;
+    MCHECK(c, cudaSetDevice(c->device));
+    if (c->copy_stream) MCHECK(c, cudaStreamSynchronize(c->copy_stream));
+    MCHECK(c, cudaStreamSynchronize(c->stream));
+    return MANTIS_OK;
 }

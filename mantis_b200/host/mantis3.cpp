@@ -3,7 +3,7 @@
 // frame (or one call for all frames with --batch), publishPose() (PosePub.h:12-61) becomes a line on
 // stdout.  main() mirrors src/mantis3.cpp:138-158: parameters -> context -> frames.
 //
-//   mantis3 --K fx,0,cx,0,fy,cy,0,0,1 [--D k1,k2,k3,k4] [--map params/map.yaml] [--device N] [--batch]
+//   mantis3 --K fx,0,cx,0,fy,cy,0,0,1 [--D k1,k2,k3,k4] [--map params/map.yaml] [--device N | --devices 0-7] [--batch]
 //           [--canny_hysteresis T] [--polygon_epsilon E] [--grid_spacing S]
 //           [--neighborhood_search_radius_multiplier M]   image.ppm | frame.bgr:WxH ...
 #include "mantis_host.h"
@@ -13,7 +13,7 @@ using namespace mantis_host;
 static void usage()
 {
     fprintf(stderr,
-            "usage: mantis3 --K k0,...,k8 [--D d0,d1,d2,d3] [--map map.yaml] [--device N] [--batch]\n"
+            "usage: mantis3 --K k0,...,k8 [--D d0,d1,d2,d3] [--map map.yaml] [--device N | --devices 0-7] [--batch]\n"
             "               [--canny_hysteresis T] [--polygon_epsilon E] [--grid_spacing S]\n"
             "               [--neighborhood_search_radius_multiplier M] image.ppm|frame.bgr:WxH ...\n");
 }
@@ -39,6 +39,7 @@ int main(int argc, char** argv)
     std::string map_path;
     std::vector<std::string> inputs;
     int device = 0;
+    std::vector<int> devices;   // --devices 0-7: the batch is sharded over several GPUs (implies --batch)
     bool have_K = false, batch = false;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -55,6 +56,7 @@ int main(int argc, char** argv)
             return 0;
         }
         else if (a == "--device") device = atoi(next());
+        else if (a == "--devices") { devices = parseDevices(next()); batch = true; }
         else if (a == "--batch") batch = true;
         else if (a == "--canny_hysteresis") cfg.canny_hysteresis = atoi(next());
         else if (a == "--polygon_epsilon") cfg.polygon_epsilon = atoi(next());
@@ -65,16 +67,18 @@ int main(int argc, char** argv)
     }
     if (!have_K || inputs.empty()) { usage(); return 2; }
 
-    mantis_ctx* ctx = nullptr;
-    int rc = mantis_create(&cfg, device, &ctx);
-    if (rc != MANTIS_OK) { fprintf(stderr, "mantis_create: %s\n", mantis_strerror(rc)); return 1; }
-    if (!map_path.empty()) {  // otherwise the library's built-in copy of params/map.yaml is used
-        Map m;
+    if (devices.empty()) devices.push_back(device);
+    Map m;
+    const bool have_map = !map_path.empty();   // otherwise the library's built-in copy of params/map.yaml is used
+    if (have_map) {
         if (!loadMapYaml(map_path, m)) { fprintf(stderr, "cannot read map %s\n", map_path.c_str()); return 1; }
-        if ((rc = applyMap(ctx, m))) { fprintf(stderr, "mantis_set_map: %s\n", mantis_strerror(rc)); return 1; }
         fprintf(stderr, "size of white map %zu\nsize of red map %zu\nsize of greenMap %zu\n", m.white.size(), m.red.size(),
                 m.green.size());
     }
+    DevicePool pool;
+    int rc = pool.open(devices, &cfg, have_map ? &m : nullptr);
+    if (rc != MANTIS_OK) { fprintf(stderr, "mantis_create: %s\n", mantis_strerror(rc)); return 1; }
+    mantis_ctx* ctx = pool.ctx(0);
 
     std::vector<Image> images(inputs.size());
     for (size_t i = 0; i < inputs.size(); ++i) {
@@ -88,8 +92,8 @@ int main(int argc, char** argv)
     bool same = true;
     for (const mantis_frame& f : frames) same = same && f.width == frames[0].width && f.height == frames[0].height;
     if (batch && same) {
-        rc = mantis_localize_batch(ctx, frames.data(), (int)frames.size(), res.data(), nullptr, MANTIS_MEM_HOST);
-        if (rc) { fprintf(stderr, "mantis_localize_batch: %s [%s]\n", mantis_strerror(rc), mantis_last_error(ctx)); return 1; }
+        rc = pool.localize(frames.data(), (int)frames.size(), 0, res.data(), nullptr, MANTIS_MEM_HOST);
+        if (rc) { fprintf(stderr, "mantis_localize_batch: %s\n", pool.error().c_str()); return 1; }
     } else {
         for (size_t i = 0; i < frames.size(); ++i) {  // one callback per image, as the node receives them
             rc = mantis_localize_batch(ctx, &frames[i], 1, &res[i], nullptr, MANTIS_MEM_HOST);
@@ -97,6 +101,5 @@ int main(int argc, char** argv)
         }
     }
     for (size_t i = 0; i < frames.size(); ++i) printPose(inputs[i].c_str(), res[i], publishPose(res[i], images[i].stamp_ns));
-    mantis_destroy(ctx);
     return 0;
 }

@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <fstream>
+#include <thread>
 #include <sstream>
 #include <string>
 #include <vector>
@@ -213,5 +214,96 @@ inline bool parseDoubles(const char* s, double* out, int n)
     }
     return true;
 }
+
+
+// "0-7", "0,2,5", "3" -> device indices
+inline std::vector<int> parseDevices(const std::string& spec)
+{
+    std::vector<int> d;
+    std::stringstream ss(spec);
+    std::string part;
+    while (std::getline(ss, part, ',')) {
+        const size_t dash = part.find('-');
+        if (dash != std::string::npos && dash > 0) {
+            const int a = atoi(part.substr(0, dash).c_str()), b = atoi(part.substr(dash + 1).c_str());
+            for (int k = a; k <= b; ++k) d.push_back(k);
+        } else if (!part.empty()) {
+            d.push_back(atoi(part.c_str()));
+        }
+    }
+    return d;
+}
+
+// Several GPUs of one box behind one call: one mantis_ctx and one host thread per device, the
+// batch cut into contiguous shards -- device g of G takes units [g n / G, (g + 1) n / G) -- and every shard's
+// records written straight into the caller's array at the shard's offset.  Frames are independent, so there is no
+// exchange between devices: no collective, no peer copies.  A unit is a frame, or a whole rig (rigs are never
+// split).  The reference serves one frame at a time on one thread (src/mantis_server.cpp:23-38).
+class DevicePool {
+public:
+    DevicePool() = default;
+    DevicePool(const DevicePool&) = delete;
+    DevicePool& operator=(const DevicePool&) = delete;
+    ~DevicePool() { close(); }
+
+    // 0 on success, else the mantis_status of the first context that could not be created
+    int open(const std::vector<int>& devices, const mantis_config* cfg, const Map* map = nullptr)
+    {
+        close();
+        for (int dev : devices) {
+            mantis_ctx* c = nullptr;
+            int rc = mantis_create(cfg, dev, &c);
+            if (rc == 0 && map) rc = applyMap(c, *map);
+            if (rc) { if (c) mantis_destroy(c); close(); return rc; }
+            ctx_.push_back(c);
+            dev_.push_back(dev);
+        }
+        return ctx_.empty() ? (int)MANTIS_ERR_INVALID : 0;
+    }
+    void close()
+    {
+        for (mantis_ctx* c : ctx_) mantis_destroy(c);
+        ctx_.clear();
+        dev_.clear();
+    }
+    int size() const { return (int)ctx_.size(); }
+    mantis_ctx* ctx(int g) const { return ctx_[g]; }
+    const std::string& error() const { return err_; }
+
+    // frames: n_units * cams_per_unit records (cams_per_unit == 0: plain frames, mantis_localize_batch);
+    // out (and trace, optional): n_units records.  Host or device frames as `mem` says -- device frames must
+    // live on the device their shard goes to, so multi-device callers normally pass host frames.
+    int localize(const mantis_frame* frames, int n_units, int cams_per_unit, mantis_result* out, mantis_frame_trace* trace,
+                 int mem)
+    {
+        const int G = size();
+        if (G == 0) return MANTIS_ERR_INVALID;
+        const int C = cams_per_unit > 0 ? cams_per_unit : 1;
+        std::vector<int> rc((size_t)G, 0);
+        auto shard = [&](int g) {
+            const int u0 = (int)((long long)n_units * g / G), u1 = (int)((long long)n_units * (g + 1) / G);
+            if (u1 <= u0) return;
+            const mantis_frame* f = frames + (size_t)u0 * C;
+            mantis_frame_trace* t = trace ? trace + u0 : nullptr;
+            rc[g] = cams_per_unit > 0 ? mantis_localize_rig_batch(ctx_[g], f, u1 - u0, C, out + u0, t, mem)
+                                      : mantis_localize_batch(ctx_[g], f, u1 - u0, out + u0, t, mem);
+        };
+        std::vector<std::thread> th;
+        for (int g = 1; g < G; ++g) th.emplace_back(shard, g);
+        shard(0);
+        for (std::thread& t : th) t.join();
+        for (int g = 0; g < G; ++g)
+            if (rc[g]) {
+                err_ = "device " + std::to_string(dev_[g]) + ": " + mantis_strerror(rc[g]) + " [" + mantis_last_error(ctx_[g]) + "]";
+                return rc[g];
+            }
+        return MANTIS_OK;
+    }
+
+private:
+    std::vector<mantis_ctx*> ctx_;
+    std::vector<int> dev_;
+    std::string err_;
+};
 
 }  // namespace mantis_host

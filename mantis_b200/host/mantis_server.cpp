@@ -37,6 +37,8 @@ struct Response {  // mantisService.srv:9-12
 
 static mantis_ctx* g_ctx;
 
+static bool g_per_camera = false;
+
 // The service handler.  Returns false on an API failure (the ROS service call would fail).
 static bool runMantis(const Request& req, Response& res)
 {
@@ -46,8 +48,27 @@ static bool runMantis(const Request& req, Response& res)
     for (int i = 0; i < n; ++i)
         frames.push_back(toFrame(req.image[i], req.camera_info[i], req.cam_to_base[i].size() == 7 ? req.cam_to_base[i].data() : nullptr));
     std::vector<mantis_result> out((size_t)n);
-    bool same = true;
+    bool same = true, rig = n > 1;
     for (const mantis_frame& f : frames) same = same && f.width == frames[0].width && f.height == frames[0].height && f.stride_bytes == frames[0].stride_bytes;
+    for (int i = 0; i < n; ++i) rig = rig && req.cam_to_base[i].size() == 7 && req.cam_to_base[i][6] * req.cam_to_base[i][6] + req.cam_to_base[i][3] * req.cam_to_base[i][3] + req.cam_to_base[i][4] * req.cam_to_base[i][4] + req.cam_to_base[i][5] * req.cam_to_base[i][5] > 0;
+    res = Response();
+    if (rig && same && n <= MANTIS_MAX_RIG_CAMERAS && !g_per_camera) {
+        // Every camera comes with its base->camera transform: the request is one rig, localized JOINTLY -- hypotheses
+        // of all cameras pooled in the base frame, every score summed over the cameras (what the reference's server
+        // states as its intent: MonteCarlo.cpp:233-241, Mantis2Error.h:55-99).  The pose is the base's.
+        mantis_result r;
+        if (mantis_localize_rig_batch(g_ctx, frames.data(), 1, n, &r, nullptr, MANTIS_MEM_HOST)) return false;
+        res.num_particles = r.n_particles;
+        PoseEstimate p = publishPose(r, req.image[0].stamp_ns);
+        if (p.published) {
+            for (int k = 0; k < 3; ++k) res.pose[k] = p.position[k];
+            for (int k = 0; k < 4; ++k) res.pose[3 + k] = p.orientation_xyzw[k];
+            res.weight = r.error;
+            res.valid = true;
+            res.best_camera = -1;   // joint
+        }
+        return true;
+    }
     if (same) {
         if (mantis_localize_batch(g_ctx, frames.data(), n, out.data(), nullptr, MANTIS_MEM_HOST)) return false;
     } else {  // one call per resolution group; here simply one per frame
@@ -57,7 +78,6 @@ static bool runMantis(const Request& req, Response& res)
     // Rig fusion: every camera that passes publishPose()'s gate votes with its pose moved into the
     // base frame (world<-base = world<-cam * (base<-cam)^-1); the lowest colour error wins.
     // (The reference computes `hyp.getW2C() * c2b` and then publishes the camera pose, PosePub.h:28-44.)
-    res = Response();
     for (int i = 0; i < n; ++i) {
         res.num_particles += out[i].n_particles;
         PoseEstimate p = publishPose(out[i], req.image[i].stamp_ns);
@@ -89,7 +109,8 @@ int main(int argc, char** argv)
         std::string a = argv[i];
         if (a == "--device" && i + 1 < argc) device = atoi(argv[++i]);
         else if (a == "--map" && i + 1 < argc) map_path = argv[++i];
-        else { fprintf(stderr, "usage: mantis_server [--device N] [--map map.yaml] < requests\n"); return 2; }
+        else if (a == "--per-camera") g_per_camera = true;   // rigs: localize every camera alone, best one wins (no joint refinement)
+        else { fprintf(stderr, "usage: mantis_server [--device N] [--map map.yaml] [--per-camera] < requests\n"); return 2; }
     }
     int rc = mantis_create(&cfg, device, &g_ctx);
     if (rc) { fprintf(stderr, "mantis_create: %s\n", mantis_strerror(rc)); return 1; }

@@ -88,8 +88,8 @@ def test_mantis3_matches_binding(ctx, tmp_path):
 
 @pytest.mark.gpu
 def test_mantis_server_rig_request(ctx, tmp_path):
-    """Two cameras of a rig looking at the same floor: the response is the better camera's pose moved into
-    the base frame (world<-base = world<-cam * (base<-cam)^-1)."""
+    """--per-camera: two cameras looking at the same floor, each localized alone; the response is the better
+    camera's pose moved into the base frame (world<-base = world<-cam * (base<-cam)^-1)."""
     W, H = 640, 480
     K, D = K_for(W, H), np.zeros(4)
     ps = poses(2, seed=777)
@@ -103,7 +103,8 @@ def test_mantis_server_rig_request(ctx, tmp_path):
     for p, cb in zip(paths, c2b):
         req += f"image {p}\nK {Ks}\nD 0 0 0 0\ncam_to_base {' '.join(map(str, cb))}\n"
     req += "delta_pos 0 0 0\ndelta_quat 0 0 0 1\nend\n"
-    out = subprocess.run([os.path.join(BIN, "mantis_server")], input=req, capture_output=True, text=True, check=True).stdout
+    out = subprocess.run([os.path.join(BIN, "mantis_server"), "--per-camera"], input=req, capture_output=True, text=True,
+                         check=True).stdout
     d = _fields(out.strip().splitlines()[-1])
     res, _ = ctx.localize(np.stack([po.render_grid(R, t, K, D, W, H) for R, t in ps]), K, D)
     assert int(d["ok"]) == 1
@@ -127,3 +128,55 @@ def test_mantis_server_rig_request(ctx, tmp_path):
         assert np.allclose(d["pose"][:3], twb, atol=1e-7)
         assert np.allclose(q2m(d["pose"][3:]), Rwb, atol=1e-7)
         assert float(d["weight"]) == pytest.approx(res[best].error, rel=1e-8)
+
+
+@pytest.mark.gpu
+def test_mantis_server_joint_rig_request(ctx, tmp_path):
+    """A request whose cameras all carry cam_to_base is ONE rig: localized jointly on the device
+    (mantis_localize_rig_batch); the response is the base pose and equals the binding's."""
+    from frames import rig_cam_to_base, rig_extrinsics
+
+    W, H = 640, 480
+    K, D = K_for(W, H), np.zeros(4)
+    ext, b2c = rig_extrinsics()[:3], rig_cam_to_base()[:3]
+    Rb, tb = poses(1, seed=778)[0]
+    frames = np.stack([po.render_grid(Rb @ Rc, tb + Rb @ tc, K, D, W, H) for Rc, tc in ext])
+    Ks = " ".join(repr(float(v)) for v in K.reshape(-1))
+    req = "request\n"
+    for i in range(3):
+        p = str(tmp_path / f"r{i}.ppm")
+        _write_ppm(p, frames[i])
+        req += f"image {p}\nK {Ks}\nD 0 0 0 0\ncam_to_base {' '.join(repr(float(v)) for v in b2c[i])}\n"
+    req += "delta_pos 0 0 0\ndelta_quat 0 0 0 1\nend\n"
+    out = subprocess.run([os.path.join(BIN, "mantis_server")], input=req, capture_output=True, text=True, check=True).stdout
+    d = _fields(out.strip().splitlines()[-1])
+    res, _ = ctx.localize_rig(frames[None], np.stack([K] * 3), np.stack([D] * 3), b2c)
+    r = res[0]
+    assert int(d["ok"]) == 1 and int(d["num_particles"]) == r.n_particles
+    assert int(d["valid"]) == int(r.status == 0 and r.min_yaw_diff > 4000)
+    if int(d["valid"]):
+        assert int(d["best_camera"]) == -1
+        assert np.allclose(d["pose"][:3], list(r.pos), atol=1e-8) and np.allclose(d["pose"][3:], list(r.quat_xyzw), atol=1e-8)
+        assert float(d["weight"]) == pytest.approx(r.error, rel=1e-8)
+
+
+@pytest.mark.gpu
+def test_device_pool_shards_give_the_single_device_records(tmp_path):
+    """mantis3 --devices: one context + one host thread per entry, contiguous shards, records in one array
+    (SURVEY 8e).  Two contexts on GPU 0 always; GPUs 0 and 1 when the box has them.  Byte-identical output."""
+    import torch
+
+    W, H = 640, 480
+    K, D = K_for(W, H), np.zeros(4)
+    paths = []
+    for i, (R, t) in enumerate(poses(7, seed=4243)):
+        paths.append(str(tmp_path / f"p{i}.ppm"))
+        _write_ppm(paths[-1], po.render_grid(R, t, K, D, W, H))
+    Ks = ",".join(repr(float(v)) for v in K.reshape(-1))
+    run = lambda *extra: subprocess.check_output([os.path.join(BIN, "mantis3"), "--K", Ks, *extra, *paths], text=True)
+    one = run("--batch")
+    assert one.count("status=") == len(paths)
+    assert run("--devices", "0,0") == one
+    assert run("--devices", "0,0,0") == one
+    if torch.cuda.device_count() >= 2:
+        assert run("--devices", "0-1") == one

@@ -241,3 +241,32 @@ def test_localize_rejects_skewed_camera_matrix(ctx):
     K[0, 1] = 0.5
     with pytest.raises(mantis_b200.MantisError, match="skew"):
         ctx.localize(np.zeros((1, 48, 64, 3), np.uint8), K, np.zeros(4))
+
+
+def test_localize_async_equals_blocking_call(ctx):
+    """mantis_localize_batch_async + mantis_wait: the same records as the blocking call, for device-resident frames
+    (several chunks queued back to back, results into pinned memory) and for host frames."""
+    import ctypes
+
+    import torch
+
+    import mantis_b200
+
+    W, H, N = 640, 480, 300
+    K, D = K_for(W, H), np.zeros(4)
+    buf = torch.empty((N, H, W, 3), dtype=torch.uint8, device="cuda:0")
+    ctx.render_grid_device(poses(N, seed=0x4D414E54 + 14), W, H, K, D, buf.data_ptr())
+    torch.cuda.synchronize()
+    dframes = ctx.make_frames([buf.data_ptr() + i * H * W * 3 for i in range(N)], W, H, K, D)
+    ref, _ = ctx.localize_frames(dframes, mantis_b200.MEM_DEVICE)
+    pinned = torch.zeros(N * ctypes.sizeof(mantis_b200.Result), dtype=torch.uint8, pin_memory=True)
+    out = (mantis_b200.Result * N).from_address(pinned.data_ptr())
+    ctx.localize_frames_async(dframes, mantis_b200.MEM_DEVICE, out)
+    ctx.wait()
+    assert bytes(out) == bytes(ref)
+    host = buf[:40].cpu().numpy()
+    hframes = ctx.make_frames([host[i] for i in range(40)], W, H, K, D)
+    out2 = (mantis_b200.Result * 40)()
+    ctx.localize_frames_async(hframes, mantis_b200.MEM_HOST, out2)
+    ctx.wait()
+    assert bytes(out2) == bytes(ref)[:40 * ctypes.sizeof(mantis_b200.Result)]
