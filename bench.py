@@ -12,6 +12,9 @@ over one batch of synthetic rendered grid frames (BASELINE.json configs[1]: 640x
             timed live with CUDA events inside the timed steps, against MEASURED_PEAKS.json's HBM figure
   cpu_baseline  the CPU oracle (a C restatement of the reference's path, kind "port") on the box's host
             cores over a bounded sample of the same frames (rank 0, N=1 only)
+  per_rank  ms per step of every rank (min / median / max): what the max-over-ranks `value` hides
+  parity_sample, hd720_frames_per_s, rig_4x720p_rigs_per_s, hd1080_noise_frames_per_s, d_nonzero_frames_per_s,
+  pnp_frames_per_s   (N = 1) the other BASELINE.json configs and a checked sample, tools/bench_extras.py
 
   --impl reference   times that CPU path alone (the reference has no GPU code and cannot be built here:
                      it needs ROS + OpenCV C++).
@@ -31,6 +34,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 METRIC = "localized frames/sec at 640x480"
 UNIT = "frames/s"
@@ -49,6 +53,8 @@ def parse():
     ap.add_argument("--cpu-reps", type=int, default=40, help="passes over the CPU sample inside its timer")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the other configs' keys and the parity sample (N = 1 only)")
+    ap.add_argument("--parity-frames", type=int, default=512, help="frames of the workload checked against the oracle")
     return ap.parse_args()
 
 
@@ -222,6 +228,14 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def all_ranks(x):
+        """x of every rank (rank order)."""
+        if dist is None:
+            return [x]
+        t = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(t, torch.tensor([x], dtype=torch.float64, device="cuda"))
+        return [float(v.item()) for v in t]
+
     B = args.batch
     K, D = K_for(W, H), np.zeros(4)
     ctx = mantis_b200.Context(local)
@@ -251,8 +265,12 @@ def main():
     barrier()
     launches = ctx.launch_count - l0
     clocks = sampler.stop()
-    ms = max_over_ranks(e0.elapsed_time(e1))
+    ms_rank = e0.elapsed_time(e1)
+    ms_all = all_ranks(ms_rank)
+    ms = max(ms_all)
     value = world * B * args.steps / (ms * 1e-3)
+    per_rank = {"ms_per_step": [m / args.steps for m in ms_all], "min": min(ms_all) / args.steps,
+                "median": statistics.median(ms_all) / args.steps, "max": max(ms_all) / args.steps}
 
     # ---- per-stage device times: the same K steps once more with the library's stage events on (CUDA events
     # on the library's stream between the stages).  The library runs one lane by default, so this pass and
@@ -296,6 +314,7 @@ def main():
 
     # ---- end to end: host (pinned) frames through the same C-ABI call ----
     e2e = None
+    host = None
     if not args.no_e2e:
         nb = B
         try:
@@ -308,29 +327,53 @@ def main():
         hframes = ctx.make_frames([host.data_ptr() + i * H * W * 3 for i in range(nb)], W, H, K, D)
         for _ in range(min(args.warmup, 2)):
             ctx.localize_frames(hframes, mantis_b200.MEM_HOST)
-        ksteps = max(1, min(args.steps, 3))
+        ksteps = max(1, args.steps)
         barrier()
         t0 = time.perf_counter()
         for _ in range(ksteps):
             hres, _ = ctx.localize_frames(hframes, mantis_b200.MEM_HOST)
         torch.cuda.synchronize()
-        dt = max_over_ranks(time.perf_counter() - t0)
+        dt_all = all_ranks(time.perf_counter() - t0)
+        dt = max(dt_all)
         e2e = {"value": world * nb * ksteps / dt, "unit": UNIT, "h2d_bytes_per_step": nb * H * W * 3,
                "d2h_bytes_per_step": nb * 72 + nb * 16, "frames_per_gpu_per_step": nb, "steps": ksteps,
+               "h2d_gb_per_s_aggregate": world * nb * H * W * 3 * ksteps / dt / 1e9,
+               "per_rank_s_per_step": [d / ksteps for d in dt_all],
                "timer": "host wall clock around the synchronous C-ABI call, max over ranks"}
         assert [r.status for r in hres[:64]] == [r.status for r in res[:64]]
+
+    # ---- the other configs and the parity sample (N = 1; each timed with CUDA events in this same run) ----
+    extras = {}
+    if world == 1 and not args.no_extras:
+        import bench_extras as bx
+        from frames import D_UNIT
+
+        host = None   # (the pinned staging buffer of the e2e arm is no longer needed)
+        torch.cuda.empty_cache()
+        if args.parity_frames > 0:
+            extras["parity_sample"] = bx.parity_sample(ctx, buf, W, H, K, D, min(args.parity_frames, B))
+        del dframes
+        buf = None
+        torch.cuda.empty_cache()
+        extras["d_nonzero_frames_per_s"] = bx.localize_rate(ctx, W, H, B, D_UNIT, SEED + 100)
+        extras["d_nonzero_frames_per_s"]["camera"] = "fx=fy=320 cx=320 cy=240, D = test/unit_test.cpp:144"
+        extras["hd720_frames_per_s"] = bx.localize_rate(ctx, 1280, 720, 1024, np.zeros(4), SEED + 101)
+        extras["rig_4x720p_rigs_per_s"] = bx.rig_rate(ctx, 1280, 720, 256, SEED + 102)
+        extras["hd1080_noise_frames_per_s"] = bx.localize_rate(ctx, 1920, 1080, 512, np.zeros(4), SEED + 103, degrade=True)
+        extras["pnp_frames_per_s"] = bx.pnp_rate(ctx)
 
     if rank == 0:
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "u8 image stages, int32 contours, f64 pose/scoring", "data": "synthetic",
                "config": workload(B, world), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
-               "roofline": roofline,
+               "roofline": roofline, "per_rank": per_rank,
                "stage_ms_per_step": {k: v / args.steps for k, v in stage.items()},
                "single_lane_ms_per_step": ms_single / args.steps, "lanes": int(os.environ.get("MANTIS_LANES", "1")),
                "frame_status_histogram": dict(zip(["ok", "no_quads", "no_hypotheses", "yaw_failed", "overflow"], status))}
         if cpu is not None:
             out["cpu_baseline"] = cpu
+        out.update(extras)
         print(json.dumps(out))
     ctx.close()
     if dist is not None:
