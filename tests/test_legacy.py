@@ -38,6 +38,68 @@ def test_oracle_markov_properties():
     assert e[0] == 2.0 / m.p[185] and e[1] > e[0]
 
 
+def _ref_markov():
+    import ctypes
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libmarkov_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libmarkov_ref.so not built (reference tree absent)")
+    L = ctypes.CDLL(path)
+    d, vp, ci = ctypes.c_double, ctypes.c_void_p, ctypes.c_int
+    L.markov_ref_update_weights.argtypes = [vp, d]
+    L.markov_ref_init.argtypes = [vp, d]
+    L.markov_ref_convolve.argtypes = [vp, d, d]
+    L.markov_ref_sense_plane.argtypes = [vp, vp]
+    L.markov_ref_update_errors.argtypes = [vp, vp, vp, ci]
+    L.markov_ref_get_yaw.argtypes = [vp]
+    L.markov_ref_get_yaw.restype = d
+    return L
+
+
+def test_oracle_markov_matches_compiled_reference():
+    """oracle/legacy.c against the reference's own include/mantis3/Markov.cpp, compiled unmodified into
+    oracle/_ref/libmarkov_ref.so (oracle/ref_build): constructor, updateWeights, convolve, senseFusion(plane),
+    updateHypothesis and getYaw on seeded sequences -- the same doubles, bit for bit."""
+    L = _ref_markov()
+    rng = np.random.default_rng(0x4D414E54 + 71)
+    for trial in range(12):
+        yaw0 = rng.uniform(-np.pi, np.pi)
+        m = po.Markov(yaw_rad=yaw0)
+        r = np.zeros(360)
+        L.markov_ref_init(r.ctypes.data, float(yaw0))
+        assert np.array_equal(m.p, r), ("init", trial)
+        for step in range(6):
+            dth, dt = rng.uniform(-2.5, 2.5), rng.uniform(0.5, 8.0)
+            m.convolve(dth, dt)
+            L.markov_ref_convolve(r.ctypes.data, float(dth), float(dt))
+            assert np.array_equal(m.p, r), ("convolve", trial, step)
+            # senseFusion(Hypothesis) cannot run in the reference (its zeroing loop never ends, Markov.cpp:190-191):
+            # the sense plane is built as that function means to, with the reference's own updateWeights
+            ys = rng.uniform(-np.pi, np.pi)
+            sense = np.zeros(360)
+            deg = ys * 180.0 / np.pi
+            sense[int(deg + 360 if deg < 0 else deg)] = 1
+            L.markov_ref_update_weights(sense.ctypes.data, 3.5)
+            L.markov_ref_sense_plane(r.ctypes.data, sense.ctypes.data)
+            m.sense(ys)
+            assert np.array_equal(m.p, r), ("sense", trial, step)
+            yaws = rng.uniform(-np.pi, np.pi, 9)
+            errs = rng.uniform(1e3, 1e5, 9)
+            e_ref = errs.copy()
+            L.markov_ref_update_errors(r.ctypes.data, yaws.ctypes.data, e_ref.ctypes.data, 9)
+            assert np.array_equal(m.update_errors(yaws, errs), e_ref), ("update_errors", trial, step)
+            assert m.get_yaw()[0] == L.markov_ref_get_yaw(r.ctypes.data)
+    # updateWeights on an arbitrary plane, several widths
+    for sd in (0.4, 3.0, 3.5, 11.0):
+        plane = rng.uniform(0, 1, 360)
+        a = po.Markov(plane=plane)
+        a.update_weights(sd)
+        b = plane.copy()
+        L.markov_ref_update_weights(b.ctypes.data, float(sd))
+        assert np.array_equal(a.p, b), sd
+
+
 def _particles(n_p, seed):
     rng = np.random.default_rng(seed)
     out = []
