@@ -22,9 +22,9 @@
 //     a' = c11 Kxx a + c12 (Kxx b + Kxy a) + c22 Kxy b      Kxx = Gxx + Gx tF Gx,  Kxy = Gxy + Gx tF Gy,
 //     b' = c11 Kxy^T a + c12 (Kxy^T b + Kyy a) + c22 Kyy b  Kyy = Gyy + Gy tF Gy.
 // A run is a chain of dependent steps and the longest runs (thousands of steps) set the duration of
-// the whole launch, so what matters is the LATENCY of a step: all matrix-vector products above
-// depend only on (a, b) and issue beside the scalar chain (a, b) -> c, after which a', b' are three
-// multiply-adds away.  R, t and the error hang off that chain.  The state of a run is (a, b, r1, r2, t).
+// the whole launch.  The a', b' form above lets every matrix-vector product issue beside the scalar chain
+// (a, b) -> c, but costs twelve products per step; the step is bound by the fp64 pipe, not by that chain, so
+// abs_kernel() forms (r1, r2) first and multiplies five matrices.  The state of a run is (a, b, r1, r2, t).
 //
 // The error that feeds the stopping rule (RPP.cpp:171, |(old - new) / old| > 1e-5) is accumulated point
 // by point from (R, t), as the reference does.  The closed quadratic form above would be cheaper, but it
@@ -229,23 +229,15 @@ __device__ __noinline__ double abs_kernel_general_impl(const double* ctx, int st
 }
 
 // One AbsKernel step (RPP.cpp:229-332): from the current points (through L.a, L.b) to R, t, the new
-// points and their error.
+// points and their error.  After the polar coefficients c the step is refresh() on the new (r1, r2):
+// five matrix-vector products (t, a', b') instead of the twelve that the a / b-only formulation issues
+// beside the scalar chain.  That formulation is ~50 cycles shorter in latency per step, but a step is bound
+// by the fp64 pipe (a warp's DFMA holds it for two cycles whatever the number of live lanes), so the
+// instruction count is what sets the duration of the longest runs.
 __device__ __forceinline__ double abs_kernel(const double* ctx, int stride, Lane& L)
 {
     const double* a = L.a;
     const double* b = L.b;
-    // products that only need (a, b): they issue beside the scalar chain below
-    double kxa[3], kxb[3], kya[3], kyb[3], kma[3], kmb[3], kta[3], ktb[3], gxa[3], gxb[3], gya[3], gyb[3];
-    symv(ctx, stride, C_KXX, a, kxa);
-    symv(ctx, stride, C_KXX, b, kxb);
-    symv(ctx, stride, C_KYY, a, kya);
-    symv(ctx, stride, C_KYY, b, kyb);
-    genv2(ctx, stride, C_KXY, a, a, kma, kta);   // Kxy a, Kxy^T a
-    genv2(ctx, stride, C_KXY, b, b, kmb, ktb);   // Kxy b, Kxy^T b
-    symv(ctx, stride, C_GX, a, gxa);
-    symv(ctx, stride, C_GX, b, gxb);
-    symv(ctx, stride, C_GY, a, gya);
-    symv(ctx, stride, C_GY, b, gyb);
     const double S11 = fma(a[2], a[2], fma(a[1], a[1], a[0] * a[0])), S22 = fma(b[2], b[2], fma(b[1], b[1], b[0] * b[0])),
                  S12 = fma(a[2], b[2], fma(a[1], b[1], a[0] * b[0]));
     const double n0 = fma(a[1], b[2], -(a[2] * b[1])), n1 = fma(a[2], b[0], -(a[0] * b[2])), n2 = fma(a[0], b[1], -(a[1] * b[0]));
@@ -255,18 +247,21 @@ __device__ __forceinline__ double abs_kernel(const double* ctx, int stride, Lane
     const double inv_s = fast_rsqrt(nn), s = nn * inv_s;
     const double inv = fast_rsqrt(fma(2.0, s, tr)) * inv_s;
     const double c11 = (S22 + s) * inv, c12 = -S12 * inv, c22 = (S11 + s) * inv;
-    double r1[3], r2[3], gs[3], t[3], an[3], bn[3];
+    double r1[3], r2[3], gs[3], t[3];
     for (int k = 0; k < 3; ++k) {
-        an[k] = fma(c22, kmb[k], fma(c12, kxb[k] + kma[k], c11 * kxa[k]));
-        bn[k] = fma(c22, kyb[k], fma(c12, ktb[k] + kya[k], c11 * kta[k]));
         r1[k] = fma(b[k], c12, a[k] * c11);
         r2[k] = fma(b[k], c22, a[k] * c12);
-        gs[k] = fma(c22, gyb[k], fma(c12, gxb[k] + gya[k], c11 * gxa[k]));   // Gx r1 + Gy r2
     }
+    symv(ctx, stride, C_GX, r1, gs);
+    symv_acc(ctx, stride, C_GY, r2, gs);
     symv(ctx, stride, C_TF, gs, t);   // t = tF * sum F_i (R P_i)
     if (t[2] < 0) return abs_kernel_general(ctx, stride, L);
+    double an[3], bn[3], ta[3], tb[3];
+    symv(ctx, stride, C_KXX, r1, an);
+    symv(ctx, stride, C_KYY, r2, bn);
+    genv2(ctx, stride, C_KXY, r2, r1, ta, tb);
     const double err2 = point_error_rt(ctx, stride, r1, r2, t);
-    for (int k = 0; k < 3; ++k) { L.r1[k] = r1[k]; L.r2[k] = r2[k]; L.t[k] = t[k]; L.a[k] = an[k]; L.b[k] = bn[k]; }
+    for (int k = 0; k < 3; ++k) { L.r1[k] = r1[k]; L.r2[k] = r2[k]; L.t[k] = t[k]; L.a[k] = an[k] + ta[k]; L.b[k] = bn[k] + tb[k]; }
     L.rays = false;
     return err2;
 }
