@@ -30,7 +30,7 @@ struct mantis_ctx {
     // scratch (grows monotonically)
     DevBuf weak, strong;      // bit planes from the candidate kernel
     DevBuf canny_bits, morph_bits;  // bit-packed results of the per-frame kernel
-    DevBuf q_pts, q_dst, q_stack, q_owner, q_pad;   // quad kernel scratch
+    DevBuf q_pts, q_dst, q_stack, q_owner, q_pad, q_tmp;   // quad kernel scratch
     DevBuf frame_quads;                      // FrameQuads[n]
     DevBuf quad_hyp, pose_offs;
     DevBuf cams, hyps, sel, pose_info, results, traces, mask_bits;  // localize scratch (per chunk)

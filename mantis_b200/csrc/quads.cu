@@ -383,6 +383,7 @@ struct QMeta {  // per frame, zeroed before every batch
     int ncand, nstart, flags, nb, nlong, ncut, fallback, ncc;
 };
 constexpr int LONG_NP = 96;   // contours with more vertices are handled by a whole warp
+constexpr int TMPV = 32;      // vertices of a piece that the first walk keeps; a piece with more is walked again by k_qemit
 constexpr int MAXLONG = MANTIS_MAX_PTS / LONG_NP + 1;
 
 struct QuadArgs {
@@ -411,6 +412,7 @@ struct QuadArgs {
     uint32_t* cut_par;    // [n][MAXCUT] hole candidates: a cut visit of the border that owns the left edge of the run left of the hole
     short* hole_owner;    // [n][MAXB] that border, for the hole borders
     uint32_t* cut_dst;    // [n][MAXCUT] (offset of the piece's vertices in its frame << 10) | border
+    short2* cut_tmp;      // [n][MAXCUT][TMPV] the first TMPV vertices of every piece, kept by k_qseg for k_qemit
     int use_cuts;
     int cut_mask;             // cut rows are y & cut_mask == 0 (CUT_ROWS - 1 up to VGA, wider spacing for larger frames)
     const uint32_t* padded;   // zero-framed copies of the planes in global memory (PadImg layout) when a plane does not fit in shared memory
@@ -773,10 +775,15 @@ __global__ void __launch_bounds__(CNT) k_qcut(QuadArgs a)
     }
 }
 
-struct SegCount {
+struct SegKeep {   // counts the vertices of a piece and keeps the first TMPV of them (out may be null: count only)
+    short2* out;
     int np;
     __device__ __forceinline__ void visit(int, int, uint32_t) {}
-    __device__ __forceinline__ void point(int, int) { ++np; }
+    __device__ __forceinline__ void point(int x, int y)
+    {
+        if (out && np < TMPV) out[np] = make_short2((short)x, (short)y);
+        ++np;
+    }
 };
 struct SegEmit {
     short2* out;
@@ -850,7 +857,10 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
         if (!(raw & 1u) && cs.has(raw >> 1)) {
             // a row cut that is also listed as a candidate: the candidate entry stands for it
         } else if (nb == 0u) {  // isolated pixel: one visit, one vertex; stands under its West side
-            if (!east) { key = ((uint32_t)pos << 3) | KEY_LTOP; end = (uint32_t)pos << 3; np = 1; }
+            if (!east) {
+                key = ((uint32_t)pos << 3) | KEY_LTOP; end = (uint32_t)pos << 3; np = 1;
+                a.cut_tmp[(base + slot) * TMPV] = make_short2((short)x, (short)y);
+            }
         } else {
             const int s = back_dir(nb, side), r0 = (s + 1) & 7;
             const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
@@ -860,7 +870,7 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
                 key = ((uint32_t)pos << 3) | (uint32_t)s;
                 if ((z & 0x10u) && cs.cand_west(x, y, nb)) key |= KEY_LTOP;
                 if ((z & 0x01u) && cs.cand_east(x, y, nb)) key |= KEY_RCAND;
-                SegCount v{0};
+                SegKeep v{a.cut_tmp + (base + slot) * TMPV, 0};
                 end = walk_piece(im, cs, x, y, s, nb, v);
                 np = v.np;
             }
@@ -876,7 +886,7 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
             const uint32_t rot = ((nbl | (nbl << 8)) >> r0) & 0xffu;
             uint32_t z = ((1u << (__ffs(rot) - 1)) - 1u) << r0;
             z = (z | (z >> 8)) & 0xffu;
-            SegCount v{0};
+            SegKeep v{nullptr, 0};
             a.cut_par[base + slot] = cs.is_cut(xl, y, nbl, z) ? (((uint32_t)(y * W + xl) << 3) | (uint32_t)sl) : walk_piece(im, cs, xl, y, sl, nbl, v);
         }
         if (np > 65535) meta->fallback = 1;
@@ -994,6 +1004,8 @@ __global__ void __launch_bounds__(LNT) k_qlink(QuadArgs a)
         if (s_key[s_start[n]] & KEY_RCAND) a.hole_owner[bbase + s_rank[n]] = (short)(a.cut_dst[base + s_par[n]] & 1023u);
 }
 
+// Vertices to their place in the frame's vertex array: a copy of what k_qseg kept for pieces of up to TMPV
+// vertices; a longer piece is walked again (the frame's plane and cut table are only staged if there is one).
 template <bool GPAD>
 __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
 {
@@ -1003,6 +1015,17 @@ __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
     if (meta->fallback || meta->flags || meta->nb == 0) return;
     const int ncut = meta->ncut;
     const size_t base = (size_t)frame * MAXCUT;
+    int any_long = 0;
+    for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
+        const uint32_t d = a.cut_dst[base + slot];
+        if (d == EMPTY) continue;
+        const int np = a.cut_np[base + slot];
+        if (np > TMPV) { any_long = 1; continue; }
+        const short2* src = a.cut_tmp + (base + slot) * TMPV;
+        short2* dst = a.pts + (size_t)frame * MANTIS_MAX_PTS + (d >> 10);
+        for (int k = 0; k < np; ++k) dst[k] = src[k];
+    }
+    if (!__syncthreads_or(any_long)) return;
     CutSet cs{s_tab, W, a.cut_mask};
     for (int i = threadIdx.x; i < TABN; i += CNT) s_tab[i] = EMPTY;
     __syncthreads();
@@ -1017,13 +1040,11 @@ __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
     else im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
     for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
         const uint32_t d = a.cut_dst[base + slot];
-        if (d == EMPTY) continue;
+        if (d == EMPTY || a.cut_np[base + slot] <= TMPV) continue;
         const uint32_t key = a.cut_key[base + slot];
         const int pos = (int)((key & KEY_STATE) >> 3), y = pos / W, x = pos - y * W;
-        const uint32_t nb = im.nbr(x, y);
         SegEmit v{a.pts + (size_t)frame * MANTIS_MAX_PTS + (d >> 10)};
-        if (nb == 0u) { v.point(x, y); continue; }
-        walk_piece(im, cs, x, y, (int)(key & 7u), nb, v);
+        walk_piece(im, cs, x, y, (int)(key & 7u), im.nbr(x, y), v);
     }
 }
 
@@ -1244,7 +1265,8 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     if ((rc = ctx_reserve(c, c->q_stack, o)) ||
         (rc = ctx_reserve(c, c->q_pts, (size_t)n * MANTIS_MAX_PTS * sizeof(short2) * 2)) ||
         (rc = ctx_reserve(c, c->q_dst, (size_t)n * (MANTIS_MAX_PTS + 2 * MAXB) * sizeof(int2))) ||
-        (rc = ctx_reserve(c, c->q_owner, (size_t)n * w * h * sizeof(uint16_t))))
+        (rc = ctx_reserve(c, c->q_owner, (size_t)n * w * h * sizeof(uint16_t))) ||
+        (rc = ctx_reserve(c, c->q_tmp, (size_t)n * MAXCUT * TMPV * sizeof(short2))))
         return rc;
     char* ar = (char*)c->q_stack.p;
     QuadArgs a;
@@ -1260,6 +1282,7 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     a.dst = a.pts + (size_t)n * MANTIS_MAX_PTS;
     a.stack = (int2*)c->q_dst.p;
     a.owner = (uint16_t*)c->q_owner.p;
+    a.cut_tmp = (short2*)c->q_tmp.p;
     a.out = d_out;
     a.eps = (double)c->cfg.polygon_epsilon;
     a.stretch = c->cfg.quad_stretch_factor;
