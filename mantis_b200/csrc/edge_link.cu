@@ -224,7 +224,8 @@ __device__ __noinline__ void morph_op(cg::cluster_group& cluster, uint32_t* src,
 // at compile time.  A thread keeps one word column j and visits rows lr = 1 + tid / WW, + LNT / WW, ... so
 // that everything that depends on j (neighbour masks, the last word's mask) is loop-invariant, and the
 // column pass reads its 2k+1 rows at immediate offsets; rows outside the image are the zero rows every plane
-// carries (PADR of them), so neither pass tests a bound.  3k+7 and 3k+5 instructions per word instead of ~45 each.
+// carries (PADR of them), so neither pass tests a bound.  3k+7 instructions per word in the row pass, about k+6 in
+// the column pass (see there).
 template <int K, int WWC>
 __device__ __forceinline__ void morph_fast_t(cg::cluster_group& cluster, uint32_t* src, uint32_t* tmp, const Band& b, bool erode,
                                              int CS)
@@ -264,7 +265,31 @@ __device__ __forceinline__ void morph_fast_t(cg::cluster_group& cluster, uint32_
     } else {
         __syncthreads();
     }
-    if (active) {
+    // Column pass.  An item is NRUN consecutive rows of one word column: its NRUN + 2K input words are loaded once
+    // into registers and every output is K three-input ORs of them -- (NRUN + 2K) / NRUN shared-memory loads per
+    // word instead of 2K + 1, which is what bounded this pass (one LDS per cycle and SM against four issue slots).
+    // The last run of a column is anchored at the last row (it overlaps its neighbour and rewrites the same values).
+    constexpr int NRUN = 10;
+    if (b.nrows >= NRUN) {
+        const int runs = (b.nrows + NRUN - 1) / NRUN;
+        for (int item = tid; item < runs * WW; item += LNT) {
+            const int q = item / WW, jj = item - q * WW;
+            const int r0 = min(1 + q * NRUN, b.nrows - NRUN + 1);
+            const uint32_t m = (jj == WW - 1) ? b.last_mask : 0xffffffffu;
+            const uint32_t* p = tmp + (r0 - K) * WW + jj;
+            uint32_t v[NRUN + 2 * K];
+#pragma unroll
+            for (int i = 0; i < NRUN + 2 * K; ++i) v[i] = p[i * WW];
+            uint32_t* o = src + r0 * WW + jj;
+#pragma unroll
+            for (int i = 0; i < NRUN; ++i) {
+                uint32_t acc = v[i];
+#pragma unroll
+                for (int d = 1; d <= K; ++d) acc |= v[i + 2 * d - 1] | v[i + 2 * d];
+                o[i * WW] = (acc ^ inv) & m;
+            }
+        }
+    } else if (active) {
         for (int lr = 1 + rb; lr <= b.nrows; lr += R) {
             const uint32_t* p = tmp + lr * WW + j;
             uint32_t acc = p[0];
@@ -411,24 +436,55 @@ __global__ void __launch_bounds__(LNT, 2) k_edge_link(LinkArgs a, int cluster_si
         if (want_morph)
             for (int i = threadIdx.x; i < nrows * WW; i += LNT) B[WW + i] = a.canny_bits[plane + (size_t)b.row0 * WW + i];
         refresh_halo(cluster, B, b, CS);
-        // t = NOT(cross-gradient(canny)) -> A
-        for (int i = threadIdx.x; i < nrows * WW; i += LNT) {
-            int lr = i / WW + 1, j = i - (lr - 1) * WW;
-            uint32_t dil = stencil<true, false>(B, b, lr, j), ero = stencil<false, false>(B, b, lr, j);
-            uint32_t t = ~(dil & ~ero);
-            if (j == WW - 1) t &= b.last_mask;
-            A[lr * WW + j] = t;
-        }
-        refresh_halo(cluster, A, b, CS);
-        // mask0 = canny | (t & ~cross-interior(t)) -> B (in place over canny: reads A and own word only)
-        for (int i = threadIdx.x; i < nrows * WW; i += LNT) {
-            int lr = i / WW + 1, j = i - (lr - 1) * WW;
-            uint32_t t = A[lr * WW + j];
-            // interior = t & up & down & left & right with 0 outside the image
-            uint32_t u = row_word(A, b, lr - 1, j, 0u), d = row_word(A, b, lr + 1, j, 0u);
-            uint32_t cl = row_word(A, b, lr, j - 1, 0u), cr = row_word(A, b, lr, j + 1, 0u);
-            uint32_t interior = t & u & d & ((t << 1) | (cl >> 31)) & ((t >> 1) | (cr << 31));
-            B[lr * WW + j] |= (t & ~interior);
+        if (CS == 1 && WW <= LNT) {
+            // One CTA holds the frame: a thread keeps one word column and strides over the rows, so that the
+            // edge-of-image cases are loop-invariant masks (j) or one comparison (first / last row); the pad rows
+            // and the words before / after a row exist in shared memory, so no load is guarded.
+            const int R = LNT / WW, rb = threadIdx.x / WW, j = threadIdx.x - rb * WW;
+            const bool act = rb < R;
+            const uint32_t lm = (j == WW - 1) ? b.last_mask : 0xffffffffu;
+            const uint32_t hasL = j > 0 ? 0xffffffffu : 0u, hasR = j + 1 < WW ? 0xffffffffu : 0u;
+            const uint32_t padR = (j + 1 == WW - 1) ? ~b.last_mask : 0u;   // unused bits of the right neighbour word
+            // t = NOT(cross-gradient(canny)) -> A   (dilation: 0 outside the image; erosion: 1 outside)
+            if (act)
+                for (int lr = 1 + rb; lr <= nrows; lr += R) {
+                    const uint32_t* p = B + lr * WW + j;
+                    const uint32_t u = p[-WW], c = p[0], d = p[WW], cl = p[-1], cr = p[1];
+                    const uint32_t dil = u | c | d | ((c << 1) | ((cl & hasL) >> 31)) | ((c >> 1) | ((cr & hasR) << 31));
+                    const uint32_t ce = c | ~lm, ue = lr == 1 ? 0xffffffffu : (u | ~lm), de = lr == nrows ? 0xffffffffu : (d | ~lm);
+                    const uint32_t cle = cl | ~hasL, cre = (cr | padR) | ~hasR;
+                    const uint32_t ero = ue & ce & de & ((ce << 1) | (cle >> 31)) & ((ce >> 1) | (cre << 31));
+                    A[lr * WW + j] = ~(dil & ~ero) & lm;
+                }
+            __syncthreads();
+            // mask0 = canny | (t & ~cross-interior(t)) -> B (in place over canny: reads A and own word only)
+            if (act)
+                for (int lr = 1 + rb; lr <= nrows; lr += R) {
+                    const uint32_t* p = A + lr * WW + j;
+                    const uint32_t t = p[0], u = lr == 1 ? 0u : p[-WW], d = lr == nrows ? 0u : p[WW];
+                    const uint32_t interior = t & u & d & ((t << 1) | ((p[-1] & hasL) >> 31)) & ((t >> 1) | ((p[1] & hasR) << 31));
+                    B[lr * WW + j] |= (t & ~interior);
+                }
+        } else {
+            // t = NOT(cross-gradient(canny)) -> A
+            for (int i = threadIdx.x; i < nrows * WW; i += LNT) {
+                int lr = i / WW + 1, j = i - (lr - 1) * WW;
+                uint32_t dil = stencil<true, false>(B, b, lr, j), ero = stencil<false, false>(B, b, lr, j);
+                uint32_t t = ~(dil & ~ero);
+                if (j == WW - 1) t &= b.last_mask;
+                A[lr * WW + j] = t;
+            }
+            refresh_halo(cluster, A, b, CS);
+            // mask0 = canny | (t & ~cross-interior(t)) -> B (in place over canny: reads A and own word only)
+            for (int i = threadIdx.x; i < nrows * WW; i += LNT) {
+                int lr = i / WW + 1, j = i - (lr - 1) * WW;
+                uint32_t t = A[lr * WW + j];
+                // interior = t & up & down & left & right with 0 outside the image
+                uint32_t u = row_word(A, b, lr - 1, j, 0u), d = row_word(A, b, lr + 1, j, 0u);
+                uint32_t cl = row_word(A, b, lr, j - 1, 0u), cr = row_word(A, b, lr, j + 1, 0u);
+                uint32_t interior = t & u & d & ((t << 1) | (cl >> 31)) & ((t >> 1) | (cr << 31));
+                B[lr * WW + j] |= (t & ~interior);
+            }
         }
         // closes of 3, 4, 5 iterations then erode 3: dilate 3, erode 3, dilate 4, erode 4, dilate 5, erode 5 + 3
         if (CS > 1) cluster.sync(); else __syncthreads();
