@@ -24,7 +24,7 @@
 // A run is a chain of dependent steps and the longest runs (thousands of steps) set the duration of
 // the whole launch.  The a', b' form above lets every matrix-vector product issue beside the scalar chain
 // (a, b) -> c, but costs twelve products per step; the step is bound by the fp64 pipe, not by that chain, so
-// abs_kernel() forms (r1, r2) first and multiplies five matrices.  The state of a run is (a, b, r1, r2, t).
+// advance_fast() forms (r1, r2) first and multiplies five matrices.  The state of a run is (a, b, r1, r2, t).
 //
 // The error that feeds the stopping rule (RPP.cpp:171, |(old - new) / old| > 1e-5) is accumulated point
 // by point from (R, t), as the reference does.  The closed quadratic form above would be cheaper, but it
@@ -228,13 +228,14 @@ __device__ __noinline__ double abs_kernel_general_impl(const double* ctx, int st
     return err2;
 }
 
-// One AbsKernel step (RPP.cpp:229-332): from the current points (through L.a, L.b) to R, t, the new
-// points and their error.  After the polar coefficients c the step is refresh() on the new (r1, r2):
-// five matrix-vector products (t, a', b') instead of the twelve that the a / b-only formulation issues
-// beside the scalar chain.  That formulation is ~50 cycles shorter in latency per step, but a step is bound
-// by the fp64 pipe (a warp's DFMA holds it for two cycles whatever the number of live lanes), so the
-// instruction count is what sets the duration of the longest runs.
-__device__ __forceinline__ double abs_kernel(const double* ctx, int stride, Lane& L)
+// The closed-form part of one AbsKernel step (RPP.cpp:229-332): from the current points (through L.a, L.b) to
+// the next R = [r1 r2 r1 x r2], t and the (a, b) of the points they give.  Nothing of L is changed; false = this step
+// needs the general SVD step (rank-deficient A, or a translation behind the camera).
+// After the polar coefficients c the step is refresh() on the new (r1, r2): five matrix-vector products (t, a', b')
+// instead of the twelve that the a / b-only formulation issues beside the scalar chain -- that formulation is ~50
+// cycles shorter in latency, but the instruction count is what a step costs.
+__device__ __forceinline__ bool advance_fast(const double* ctx, int stride, const Lane& L, double* r1, double* r2, double* t,
+                                             double* an, double* bn)
 {
     const double* a = L.a;
     const double* b = L.b;
@@ -242,12 +243,12 @@ __device__ __forceinline__ double abs_kernel(const double* ctx, int stride, Lane
                  S12 = fma(a[2], b[2], fma(a[1], b[1], a[0] * b[0]));
     const double n0 = fma(a[1], b[2], -(a[2] * b[1])), n1 = fma(a[2], b[0], -(a[0] * b[2])), n2 = fma(a[0], b[1], -(a[1] * b[0]));
     const double nn = fma(n2, n2, fma(n1, n1, n0 * n0)), tr = S11 + S22;
-    if (!(nn > 1e-20 * (tr * tr))) return abs_kernel_general(ctx, stride, L);  // s <= 1e-10 tr
+    const bool full_rank = nn > 1e-20 * (tr * tr);   // else s <= 1e-10 tr
     // 1/s and 1/k from the reciprocal-square-root seed + two Newton steps (no sqrt, no division)
     const double inv_s = fast_rsqrt(nn), s = nn * inv_s;
     const double inv = fast_rsqrt(fma(2.0, s, tr)) * inv_s;
     const double c11 = (S22 + s) * inv, c12 = -S12 * inv, c22 = (S11 + s) * inv;
-    double r1[3], r2[3], gs[3], t[3];
+    double gs[3], ta[3], tb[3];
     for (int k = 0; k < 3; ++k) {
         r1[k] = fma(b[k], c12, a[k] * c11);
         r2[k] = fma(b[k], c22, a[k] * c12);
@@ -255,15 +256,11 @@ __device__ __forceinline__ double abs_kernel(const double* ctx, int stride, Lane
     symv(ctx, stride, C_GX, r1, gs);
     symv_acc(ctx, stride, C_GY, r2, gs);
     symv(ctx, stride, C_TF, gs, t);   // t = tF * sum F_i (R P_i)
-    if (t[2] < 0) return abs_kernel_general(ctx, stride, L);
-    double an[3], bn[3], ta[3], tb[3];
     symv(ctx, stride, C_KXX, r1, an);
     symv(ctx, stride, C_KYY, r2, bn);
     genv2(ctx, stride, C_KXY, r2, r1, ta, tb);
-    const double err2 = point_error_rt(ctx, stride, r1, r2, t);
-    for (int k = 0; k < 3; ++k) { L.r1[k] = r1[k]; L.r2[k] = r2[k]; L.t[k] = t[k]; L.a[k] = an[k] + ta[k]; L.b[k] = bn[k] + tb[k]; }
-    L.rays = false;
-    return err2;
+    for (int k = 0; k < 3; ++k) { an[k] += ta[k]; bn[k] += tb[k]; }
+    return full_rank && !(t[2] < 0);
 }
 
 // ObjPose with an initial rotation (RPP.cpp:98-128): t from R, Q_i, and the starting error.
@@ -296,15 +293,27 @@ __device__ inline void finalize(const double* ctx, int stride, const Lane& L, do
 
 // ---- one ObjPose run as a resumable state machine (RPP.cpp:66-208) --------------------------------
 // run_begin() after setup(); then run_step() until it returns true; then finalize().
+//
+// The reference's loop is  step k -> error of step k -> stop test -> step k + 1,  one dependent chain of ~60 fp64
+// operations per step, and a lone warp in the tail of the launch issues one of them every ~8 cycles.  Here a trip
+// of run_step() computes the error of the COMMITTED step k - 1 and, beside it, step k from the same state (the
+// two do not depend on each other); the stop test of step k - 1 then decides whether step k is committed or
+// thrown away.  The tests, their order and the state a run ends in are the reference's; a run costs one trip more.
 struct Run {
     double old_err, new_err;
-    int it;        // stop tests made so far
-    int pending;   // 2: the next step gives old_err (run without initial R), 1: next step gives the first new_err
+    double e_known;  // error of the committed step when it came with the step (general SVD step)
+    int it;          // stop tests made so far
+    int pending;     // 2: the next error is old_err (run without initial R), 1: the next error is the first new_err
+    bool have;       // L.(r1, r2, t) is a step whose error has not been looked at yet
+    bool known;      // ... and that error is e_known
 };
 __device__ __forceinline__ void run_begin(const double* ctx, int stride, Lane& L, Run& S, const double* initR9)
 {
     S.it = 0;
     S.new_err = 0;
+    S.e_known = 0;
+    S.have = false;
+    S.known = false;
     if (initR9) {
         S.old_err = init_from_R(ctx, stride, initR9, L);
         S.pending = 1;
@@ -313,20 +322,36 @@ __device__ __forceinline__ void run_begin(const double* ctx, int stride, Lane& L
         S.pending = 2;  // the run starts from the rays themselves (setup)
     }
 }
-// One AbsKernel step and the reference's stopping rule.  Returns true when the run is over.
+// One trip: the reference's stopping rule on the committed step, and the next AbsKernel step.  Returns true when
+// the run is over (L then holds the step the rule stopped at).
 __device__ __forceinline__ bool run_step(const double* ctx, int stride, Lane& L, Run& S, double TOL, double EPSILON)
 {
-    const double e = abs_kernel(ctx, stride, L);
-    if (S.pending == 2) {
-        S.old_err = e;
-        S.pending = 1;
-        return false;
+    const double e_calc = point_error_rt(ctx, stride, L.r1, L.r2, L.t);   // (of no use while !S.have: finite garbage)
+    double r1[3], r2[3], t[3], an[3], bn[3];
+    const bool ok = advance_fast(ctx, stride, L, r1, r2, t, an, bn);
+    if (S.have) {
+        const double e = S.known ? S.e_known : e_calc;
+        if (S.pending == 2) {
+            S.old_err = e;
+            S.pending = 1;
+        } else {
+            if (S.pending == 0) S.old_err = S.new_err;
+            S.new_err = e;
+            S.pending = 0;
+            // |(old - new) / old| > TOL without the division
+            if (!(fabs(S.old_err - S.new_err) > TOL * fabs(S.old_err) && S.new_err > EPSILON) || ++S.it > 100000) return true;
+        }
     }
-    if (S.pending == 0) S.old_err = S.new_err;
-    S.new_err = e;
-    S.pending = 0;
-    // |(old - new) / old| > TOL without the division
-    return !(fabs(S.old_err - S.new_err) > TOL * fabs(S.old_err) && S.new_err > EPSILON) || ++S.it > 100000;
+    if (ok) {
+        for (int k = 0; k < 3; ++k) { L.r1[k] = r1[k]; L.r2[k] = r2[k]; L.t[k] = t[k]; L.a[k] = an[k]; L.b[k] = bn[k]; }
+        L.rays = false;
+        S.known = false;
+    } else {
+        S.e_known = abs_kernel_general(ctx, stride, L);
+        S.known = true;
+    }
+    S.have = true;
+    return false;
 }
 
 #undef RPPF_C
