@@ -232,7 +232,10 @@ __global__ void __launch_bounds__(PNT) k_pose_select(PoseArgs a, int round)
 // Mantis2Error.h:67-68's setW2C(hyp.getW2C() * b2c)) and pooled in camera order before the clustering.  The unit's
 // pool / selection live in the slots of its first frame onwards (capacity cams_per_unit * MANTIS_MAX_HYPS); its
 // totals (n_hyps_generated, n_sel) go to the FramePose of its first frame.
-__global__ void __launch_bounds__(PNT) k_pose_cluster(PoseArgs a)
+#ifndef CLUSTER_CTAS
+#define CLUSTER_CTAS 8   // 64 registers: the kernel waits on barriers (one greedy seed after the other), more resident CTAs hide them
+#endif
+__global__ void __launch_bounds__(PNT, CLUSTER_CTAS) k_pose_cluster(PoseArgs a)
 {
     extern __shared__ __align__(16) unsigned char s_dyn[];
     const int C = a.cams_per_unit, cap = C * MANTIS_MAX_HYPS;
@@ -320,15 +323,18 @@ __global__ void __launch_bounds__(PNT) k_pose_cluster(PoseArgs a)
             s_member[j] = m;
         }
         __syncthreads();
-        if (tid == 0) {  // float accumulation in index order, as getClusterCenter does
-            float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+        if (tid < 3) {  // float accumulation in index order, as getClusterCenter does: one lane per coordinate,
+                        // branch-free (x + 0.0f == x), so that the loads run ahead of the dependent additions
+            float c = 0.f;
             int cnt = 0;
-            for (int j = 0; j < nh; ++j)
-                if (s_member[j]) { c0 += s_ang[j][0]; c1 += s_ang[j][1]; c2 += s_ang[j][2]; ++cnt; }
-            s_center[0] = (float)((double)c0 / (double)cnt);
-            s_center[1] = (float)((double)c1 / (double)cnt);
-            s_center[2] = (float)((double)c2 / (double)cnt);
-            s_cnt = 0;
+#pragma unroll 8
+            for (int j = 0; j < nh; ++j) {
+                const bool m = s_member[j];
+                c += m ? s_ang[j][tid] : 0.0f;
+                cnt += m ? 1 : 0;
+            }
+            s_center[tid] = (float)((double)c / (double)cnt);
+            if (tid == 0) s_cnt = 0;
         }
         __syncthreads();
         int local = 0;
