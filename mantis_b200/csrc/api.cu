@@ -96,7 +96,7 @@ int mantis_destroy(mantis_ctx* c)
     DevBuf* bufs[] = {&c->weak, &c->strong, &c->canny_bits, &c->morph_bits, &c->stage_in, &c->stage_in2, &c->stage_out0,
                       &c->stage_out1, &c->q_pts, &c->q_dst, &c->q_stack, &c->q_owner, &c->q_pad, &c->q_tmp, &c->frame_quads,
                       &c->cams, &c->hyps, &c->sel, &c->pose_info, &c->results, &c->traces, &c->mask_bits,
-                      &c->d_map, &c->d_rand, &c->d_shifts, &c->render_poses, &c->quad_hyp, &c->pose_offs,
+                      &c->d_map, &c->d_rand, &c->d_shifts, &c->d_shift_pts, &c->d_shift_idx, &c->render_poses, &c->quad_hyp, &c->pose_offs,
                       &c->hough_trig, &c->hough_count, &c->hough_peaks, &c->hough_lines, &c->d_atan, &c->search_ticket, &c->rig_tf, &c->pnp_stage, &c->leg_a, &c->leg_b, &c->leg_c};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);

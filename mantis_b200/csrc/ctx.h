@@ -40,6 +40,9 @@ struct mantis_ctx {
     DevBuf pnp_stage;                        // host-caller staging of mantis_pnp_batch
     DevBuf hough_trig, hough_count, hough_peaks, hough_lines;  // line-voting stage (hough.cu)
     DevBuf d_map, d_rand, d_shifts;          // world map, perturbation table, cell shifts
+    DevBuf d_shift_pts, d_shift_idx;         // the shift hypotheses through the map's lattice (search.cu: score_points)
+    int n_shift_pts = 0;                     // 0: the map is no lattice for these shifts, every shift is projected on its own
+    std::vector<double> host_shifts;         // [n_shift][2]
     int n_map = 0, n_green = 0, n_shift = 0;
     // two-lane execution of large device-resident batches (localize.cu): child contexts with their own
     // streams and scratch, so that the latency-bound kernels of one half overlap the other half's

@@ -4,6 +4,7 @@
 #include <stdlib.h>
 #include <new>
 #include <thread>
+#include <map>
 #include <vector>
 #include "ctx.h"
 #include "cvrng.h"
@@ -67,6 +68,7 @@ int ctx_init_tables(mantis_ctx* c)
     for (double x = -half + gs / 2.0; x < half; x += gs)
         for (double y = -half + gs / 2.0; y < half; y += gs) { sh.push_back(x); sh.push_back(y); }
     c->n_shift = (int)(sh.size() / 2);
+    c->host_shifts = sh;
     if ((rc = upload(c, c->d_shifts, sh.data(), sizeof(double) * sh.size()))) return rc;
 
     {   // table of the fast atan in search.cu, rounded from long double
@@ -83,6 +85,54 @@ int ctx_init_tables(mantis_ctx* c)
     int nw, nr, ng;
     default_map(c->cfg.grid_spacing, xyz, nw, nr, ng);
     return mantis_set_map(c, xyz.data(), nw, nr, ng);
+}
+
+// The shift hypotheses see map point p at p - shift (search.cu: score_points).  On a grid map most of those
+// n_shift x n_map points coincide: list the distinct ones (to 1e-10 m; representatives are the first p - shift met,
+// computed in double like any of them) and, per (shift, map point), the index of its representative, padded to
+// whole warps with the index of an always-empty table entry.  A map that does not fold (more distinct points
+// than the kernel's table holds) leaves n_shift_pts = 0 and every shift is projected on its own.
+static int build_shift_tables(mantis_ctx* c)
+{
+    c->n_shift_pts = 0;
+    const int n = c->n_map, ns = c->n_shift;
+    if (n <= 0 || ns <= 0 || (int)c->host_shifts.size() < 2 * ns) return MANTIS_OK;
+    constexpr int CAP = 6399;   // search.cu: SHIFT_PT_CAP
+    const int chunks = (n + 31) / 32;
+    struct Key { long long x, y, z; bool operator<(const Key& o) const { return x != o.x ? x < o.x : y != o.y ? y < o.y : z < o.z; } };
+    std::map<Key, int> seen;
+    std::vector<double> pts;
+    std::vector<unsigned short> idx((size_t)ns * chunks * 32);
+    for (int k = 0; k < ns; ++k) {
+        const double sx = c->host_shifts[2 * k], sy = c->host_shifts[2 * k + 1];
+        for (int i = 0; i < n; ++i) {
+            const double x = c->host_map[3 * i] - sx, y = c->host_map[3 * i + 1] - sy, z = c->host_map[3 * i + 2];
+            if (!(fabs(x) < 1e6 && fabs(y) < 1e6 && fabs(z) < 1e6)) return MANTIS_OK;
+            const Key key{llround(x * 1e10), llround(y * 1e10), llround(z * 1e10)};
+            auto it = seen.find(key);
+            int q;
+            if (it == seen.end()) {
+                q = (int)(pts.size() / 3);
+                if (q >= CAP) return MANTIS_OK;
+                seen.emplace(key, q);
+                pts.push_back(x); pts.push_back(y); pts.push_back(z);
+            } else {
+                q = it->second;
+            }
+            idx[((size_t)k * chunks) * 32 + i] = (unsigned short)q;
+        }
+    }
+    const int nq = (int)(pts.size() / 3);
+    // not worth a table unless it folds at least 4 : 1
+    if ((long long)nq * 4 > (long long)ns * n) return MANTIS_OK;
+    for (int k = 0; k < ns; ++k)
+        for (int i = n; i < chunks * 32; ++i) idx[((size_t)k * chunks) * 32 + i] = (unsigned short)nq;
+    int rc;
+    if ((rc = upload(c, c->d_shift_pts, pts.data(), sizeof(double) * pts.size())) ||
+        (rc = upload(c, c->d_shift_idx, idx.data(), sizeof(unsigned short) * idx.size())))
+        return rc;
+    c->n_shift_pts = nq;
+    return MANTIS_OK;
 }
 
 extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int n_red, int n_green)
@@ -102,7 +152,7 @@ extern "C" int mantis_set_map(mantis_ctx* c, const double* xyz, int n_white, int
     c->map_planar = 1;
     for (int i = 0; i < n; ++i)
         if (xyz[3 * i + 2] != 0.0) c->map_planar = 0;
-    return MANTIS_OK;
+    return build_shift_tables(c);
 }
 
 // quadDetection() for n frames.  rig_cams == 0: every frame on its own (mantis_localize_batch).  rig_cams >= 1: the frames

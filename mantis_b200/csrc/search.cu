@@ -18,6 +18,8 @@
 // phase of a frame goes through one inlined copy of that loop (phase loop in k_search).
 // The Gaussian perturbations of the refinement are a fixed table: the reference draws them from
 // cv::RNG(1), here re-seeded per frame, so they are the same for every frame of a context.
+#include <cstddef>
+#include <cstdlib>
 #include "ctx.h"
 #include "fastmath.cuh"
 #include "posemath.cuh"
@@ -145,6 +147,11 @@ struct SearchArgs {
     const Tf* rand_tf;  // [iterations * particles]
     const double* shifts;  // [n_shift][2]
     int n_shift, iterations, particles;
+    // the shift hypotheses through the map's lattice (localize.cu: build_shift_tables): the distinct points p - shift,
+    // and for (shift, map point) which of them it is.  n_shift_pts == 0: every shift is scored like any other hypothesis
+    const double* shift_pts;          // [n_shift_pts][3]
+    const unsigned short* shift_idx;  // [n_shift][chunks * 32], padded with n_shift_pts
+    int n_shift_pts;
     double Wd, Hd;
     unsigned* ticket; int n;
     int mask_in_smem;  // the frame's mask plane fits behind `Shared` in dynamic shared memory
@@ -355,6 +362,96 @@ __device__ __forceinline__ void score_loop(Shared& s, const SearchArgs& a, int n
     }
 }
 
+// ---- the shift hypotheses (HypothesisGeneration.h:111-140) without their 81 x n_map projections ----------------
+// Shift k moves the camera by (sx, sy, 0) in the world: c2w_k p = R^T (p - (t + s_k)) = c2w_best (p - s_k).  On a
+// grid map the points p - s_k of all shifts are a small set (2160 distinct points for 81 x 720 on the default map):
+// each of them is projected and scored ONCE under the best pose (score_points), and a shift's sums are gathers
+// from that table (shift_sums).  The projection of p - s_k differs from the reference's R^T p - R^T (t + s_k) by a few
+// ulps of the camera coordinates (~1e-13 px), so a rounding decision can only differ for a coordinate within
+// 1e-13 px of a half -- the same class of difference as the fast reciprocal / atan blocks of project_bf, and
+// checked the same way (tests/test_parity_full_gpu.py compares all 81 shift errors of every frame with the oracle).
+constexpr int SHIFT_PT_CAP = 6399;   // table entries: green_acc + green_xy of `Shared` (not live in this phase)
+static_assert(offsetof(Shared, green_xy) == offsetof(Shared, green_acc) + sizeof(unsigned int) * 80 * 40, "the table spans both arrays");
+static_assert((SHIFT_PT_CAP + 1) * sizeof(uint32_t) <= 2 * sizeof(unsigned int) * 80 * 40, "table capacity");
+
+// E[q] = 0 for a point that does not project into the frame, else 1 << 31 | its colour error on the masked image
+template <bool PLANAR, bool DIST>
+__device__ __forceinline__ void score_points(Shared& s, const SearchArgs& a, const Tf* c2w, uint32_t* E)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double2* const wp = s.wpose[warp];
+    __syncwarp();
+    if (lane < 3) wp[lane] = make_double2(c2w->R[lane * 3], c2w->R[lane * 3 + 1]);
+    else if (lane == 3) wp[3] = make_double2(c2w->t[0], c2w->t[1]);
+    else if (lane == 4) wp[4] = make_double2(c2w->t[2], 0.0);
+    else if (!PLANAR && lane == 5) wp[5] = make_double2(c2w->R[2], c2w->R[5]);
+    else if (!PLANAR && lane == 6) wp[6] = make_double2(c2w->R[8], 0.0);
+    __syncwarp();
+    const int nq = a.n_shift_pts, W = a.W, H = a.H;
+    const uint8_t* const bgr_al = s.gat.bgr_al;
+    const uint32_t* const mask = s.gat.mask;
+    const unsigned delta = s.gat.delta;
+    for (int base = warp * 32; base < nq; base += NWARP * 32) {
+        const int qi = base + lane;
+        double px = 0, py = 0, pz = 0;
+        if (qi < nq) { px = __ldg(a.shift_pts + 3 * qi); py = __ldg(a.shift_pts + 3 * qi + 1); pz = __ldg(a.shift_pts + 3 * qi + 2); }
+        double u, v;
+        bool ok = project_bf<PLANAR, DIST>(wp, s.sf, px, py, PLANAR ? 0.0 : pz, s.atan_tab, a.Wd, a.Hd, u, v);
+        ok = ok && qi < nq;
+        const int x = __double2int_rn(u), y = __double2int_rn(v);  // ok implies x >= 0, y >= 0
+        uint32_t val = 0u;
+        if (ok && x < W && y < H) {
+            uint32_t w0 = 0u, w1 = 0u;   // zero = masked out = black
+            const unsigned o = (unsigned)y * (unsigned)a.stride + 3u * (unsigned)x + delta;
+            if ((mask[(unsigned)y * (unsigned)a.WW + ((unsigned)x >> 5)] >> (x & 31)) & 1u) {
+                const uint32_t* p = reinterpret_cast<const uint32_t*>(bgr_al + (o & ~3u));
+                w0 = __ldg(p);
+                if (o & 2u) w1 = __ldg(p + 1);
+            }
+            const uint32_t inv = ~__funnelshift_r(w0, w1, (o & 3u) << 3) & 0xffffffu;
+            val = 0x80000000u | __dp4a(inv, inv, 0u);
+        } else if (ok) {  // x == W or y == H: the reference's linear addressing
+            val = 0x80000000u | (uint32_t)pixel_err(s.img, x, y, true, 255, 255, 255);
+        }
+        if (qi < nq) E[qi] = val;
+    }
+    if (threadIdx.x == 0) E[nq] = 0u;   // what the padding of shift_idx points at
+}
+
+// s.sum / s.cnt of the n_shift hypotheses from the table (one warp task = 32 map points of one shift, as in
+// score_loop; up to four tasks of one shift at a time so that their index loads are in flight together)
+__device__ __forceinline__ void shift_sums(Shared& s, const SearchArgs& a, const uint32_t* E)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int chunks = (a.n_map + 31) >> 5, total = a.n_shift * chunks;
+    const int per = (total + NWARP - 1) / NWARP, t_begin = min(warp * per, total), t_end = min(t_begin + per, total);
+    int h = t_begin / chunks, ch = t_begin - h * chunks;
+    unsigned e_acc = 0, ok_acc = 0;
+    for (int t = t_begin; t < t_end;) {
+        const int nb = min(4, min(chunks - ch, t_end - t));  // warp-uniform
+        const unsigned short* ip = a.shift_idx + (size_t)t * 32 + lane;
+        unsigned q[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) q[b] = b < nb ? (unsigned)__ldg(ip + b * 32) : (unsigned)a.n_shift_pts;   // (that entry is empty)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const uint32_t v = E[q[b]];
+            e_acc += v & 0x7fffffffu;
+            ok_acc += v >> 31;
+        }
+        ch += nb; t += nb;
+        if (ch == chunks || t == t_end) {
+            const unsigned e = __reduce_add_sync(0xffffffffu, e_acc), okw = __reduce_add_sync(0xffffffffu, ok_acc);
+            if (lane == 0 && okw) {
+                atomicAdd(&s.cnt[h], (int)okw);
+                if (e) atomicAdd(&s.sum[h], (unsigned long long)e);
+            }
+            e_acc = 0; ok_acc = 0;
+            if (ch == chunks) { ch = 0; ++h; }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -502,7 +599,16 @@ __global__ void __launch_bounds__(SNT, 1) k_search(SearchArgs a)
         }
         for (int i = tid; i < nh; i += SNT) { s.sum[i] = 0ull; s.cnt[i] = 0; }
         __syncthreads();
-        if (mode == 2) score_loop<true, false>(s, a, nh, tf_base, tf_stride, selp);
+        if (ph == a.iterations + 1 && a.n_shift_pts > 0) {
+            uint32_t* E = reinterpret_cast<uint32_t*>(s.green_acc);   // green_acc + green_xy: SHIFT_PT_CAP + 1 entries
+            if (mode == 2) score_points<true, false>(s, a, &s.best.c2w, E);
+            else if (mode == 3) score_points<true, true>(s, a, &s.best.c2w, E);
+            else if (mode == 0) score_points<false, false>(s, a, &s.best.c2w, E);
+            else score_points<false, true>(s, a, &s.best.c2w, E);
+            __syncthreads();
+            shift_sums(s, a, E);
+        }
+        else if (mode == 2) score_loop<true, false>(s, a, nh, tf_base, tf_stride, selp);
         else if (mode == 3) score_loop<true, true>(s, a, nh, tf_base, tf_stride, selp);
         else if (mode == 0) score_loop<false, false>(s, a, nh, tf_base, tf_stride, selp);
         else score_loop<false, true>(s, a, nh, tf_base, tf_stride, selp);
@@ -972,6 +1078,10 @@ static int launch_search_impl(mantis_ctx* c, const uint8_t* d_bgr, size_t pitch,
     a.rand_tf = (const Tf*)c->d_rand.p;
     a.shifts = (const double*)c->d_shifts.p;
     a.n_shift = c->n_shift; a.iterations = c->cfg.iterations; a.particles = c->cfg.particles;
+    static const bool direct_shifts = getenv("MANTIS_DIRECT_SHIFTS") != nullptr;   // (for tests: every shift projected on its own)
+    a.n_shift_pts = (rig_cams > 0 || direct_shifts) ? 0 : c->n_shift_pts;
+    a.shift_pts = (const double*)c->d_shift_pts.p;
+    a.shift_idx = (const unsigned short*)c->d_shift_idx.p;
     a.rotz = c->rotz;
     a.projection_bias = c->cfg.projection_bias;
     a.color_bias = c->cfg.color_projection_bias;
