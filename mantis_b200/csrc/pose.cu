@@ -60,18 +60,23 @@ __device__ __forceinline__ void model_xy(double s, int ordering, double* m)
     for (int k = 0; k < 4; ++k) { m[2 * k] = sx[ordering][k] * s; m[2 * k + 1] = sy[ordering][k] * s; }
 }
 
-// ---- 1. undistort the test points, queue every quad with both corner orderings ------------------
-// The reference tries the second ordering only when the first one puts the camera under the floor
-// (HypothesisGeneration.h:62-80); that is most quads, and a second round of runs would wait once
-// more for its longest run, so both orderings are solved in one round and k_pose_select applies the
-// reference's rule to the two results.
+// ---- 1. undistort the test points, queue every quad ---------------------------------------------
+// The reference solves the second corner ordering when the first one puts the camera under the floor
+// (HypothesisGeneration.h:62-80), which is most quads.  The two models differ by the sign of y
+// (gridSquarePossibilities, Mantis3Params.h:102-123) and the model is planar, so (R, t) solves ordering 0 exactly
+// when (R diag(1, -1, -1), t) solves ordering 1: same points R P_i + t, same errors, the camera mirrored through
+// the floor.  Every step of RPP keeps that symmetry (sums, polar factor, the second-pose quartic), so ordering 1
+// is not run at all: k_pose_select mirrors the result of ordering 0.  Measured on the quads of 1024 rendered
+// frames (tools/rpp_emul/mirror.py, 56 395 quads): the independently iterated ordering 1 and the mirror agree to 4e-16 (device code) /
+// 7e-15 (oracle) with the same iteration counts in every run, a tenth of the distance between the device's and
+// the oracle's RPP anyway.
 __global__ void __launch_bounds__(PNT) k_pose_prep(PoseArgs a)
 {
     __shared__ int s_base;
     const int frame = blockIdx.x, tid = threadIdx.x;
     const FrameQuads* fq = a.quads + frame;
     const int nq = fq->flags ? 0 : fq->n_quads;
-    if (tid == 0) s_base = nq ? atomicAdd(&a.cnt->n_t1[0], 2 * nq) : 0;
+    if (tid == 0) s_base = nq ? atomicAdd(&a.cnt->n_t1[0], nq) : 0;
     __syncthreads();
     const pm::Camera cam = a.cams[frame];
     for (int q = tid; q < nq; q += PNT) {
@@ -79,8 +84,7 @@ __global__ void __launch_bounds__(PNT) k_pose_prep(PoseArgs a)
         for (int k = 0; k < 4; ++k)
             pm::fisheye_undistort(cam, fq->test_px[q][2 * k], fq->test_px[q][2 * k + 1], a.rays[(size_t)id * 8 + 2 * k],
                                   a.rays[(size_t)id * 8 + 2 * k + 1]);
-        a.list1[s_base + 2 * q] = id * 2;
-        a.list1[s_base + 2 * q + 1] = id * 2 + 1;
+        a.list1[s_base + q] = id * 2;   // (entry = quad * 2 + ordering; only ordering 0 is queued)
     }
 }
 
@@ -181,46 +185,45 @@ __global__ void __launch_bounds__(PNT, SECOND_CTAS) k_pose_second(PoseArgs a, in
     }
 }
 
-// ---- 4. best candidate -> hypothesis; a wrong-side solution of ordering 0 hands over to ordering 1 ----
+// ---- 4. best candidate -> hypothesis; a wrong-side solution of ordering 0 hands over to (the mirror that is) ordering 1 ----
 __global__ void __launch_bounds__(PNT) k_pose_select(PoseArgs a, int round)
 {
     const int ntask = a.cnt->n_t1[round];
     const int* list = a.list1 + (size_t)round * a.cap;
     for (int i = blockIdx.x * PNT + threadIdx.x; i < ntask; i += gridDim.x * PNT) {
-        if (list[i] & 1) continue;  // one thread per quad: the entry of ordering 0
-        const int id = list[i] >> 1;
+        const int entry = list[i], id = entry >> 1;   // one thread per quad: the entry of ordering 0
         const int frame = id / MANTIS_MAX_QUADS, q = id - frame * MANTIS_MAX_QUADS;
         FramePose* info = a.info + frame;
-        for (int ordering = 0; ordering < 2; ++ordering) {
-            const int entry = id * 2 + ordering;
-            const int ns = a.ncand[entry];
-            int best = -1;
-            double lowest = 1e6;
-            for (int c = 0; c < ns; ++c) {
-                const double oe = a.run2[(size_t)entry * 4 + c].obj_err;
-                if (oe < lowest) { lowest = oe; best = c; }
-            }
-            if (best < 0) {  // RPP::Rpp returned false: no further ordering is tried (HypothesisGeneration.h:62-66)
-                info->quad_img_err[q] = 1.7976931348623157e308;
-                info->quad_pass[q] = 0;
-                break;
-            }
-            const RunOut& r = a.run2[(size_t)entry * 4 + best];
-            Tf c2w;
-            for (int k = 0; k < 9; ++k) c2w.R[k] = r.R[k];
-            for (int k = 0; k < 3; ++k) c2w.t[k] = r.t[k];
-            Hyp h0;
+        const int ns = a.ncand[entry];
+        int best = -1;
+        double lowest = 1e6;
+        for (int c = 0; c < ns; ++c) {
+            const double oe = a.run2[(size_t)entry * 4 + c].obj_err;
+            if (oe < lowest) { lowest = oe; best = c; }
+        }
+        if (best < 0) {  // RPP::Rpp returned false: no further ordering is tried (HypothesisGeneration.h:62-66)
+            info->quad_img_err[q] = 1.7976931348623157e308;
+            info->quad_pass[q] = 0;
+            continue;
+        }
+        const RunOut& r = a.run2[(size_t)entry * 4 + best];
+        Tf c2w;
+        for (int k = 0; k < 9; ++k) c2w.R[k] = r.R[k];
+        for (int k = 0; k < 3; ++k) c2w.t[k] = r.t[k];
+        Hyp h0;
+        pm::hyp_set_c2w(h0, c2w);
+        if (!(h0.w2c.t[2] >= 0)) {
+            // camera under the floor: the other ordering decides, and its solution is this one mirrored (see k_pose_prep)
+            for (int k = 0; k < 3; ++k) { c2w.R[3 * k + 1] = -c2w.R[3 * k + 1]; c2w.R[3 * k + 2] = -c2w.R[3 * k + 2]; }
             pm::hyp_set_c2w(h0, c2w);
-            if (ordering == 0 && !(h0.w2c.t[2] >= 0)) continue;  // camera under the floor: the other ordering decides
-            const double error = r.img_err;
-            const bool pass = !(error > a.max_quad_error);
-            info->quad_img_err[q] = error;
-            info->quad_pass[q] = pass;
-            if (pass) {
-                h0.error = 0;
-                a.quad_hyp[(size_t)id] = h0;
-            }
-            break;
+        }
+        const double error = r.img_err;
+        const bool pass = !(error > a.max_quad_error);
+        info->quad_img_err[q] = error;
+        info->quad_pass[q] = pass;
+        if (pass) {
+            h0.error = 0;
+            a.quad_hyp[(size_t)id] = h0;
         }
     }
 }

@@ -270,3 +270,41 @@ def test_localize_async_equals_blocking_call(ctx):
     ctx.localize_frames_async(hframes, mantis_b200.MEM_HOST, out2)
     ctx.wait()
     assert bytes(out2) == bytes(ref)[:40 * ctypes.sizeof(mantis_b200.Result)]
+
+
+_SHIFT_CHILD = r"""
+import ctypes, sys
+import numpy as np, torch
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+import mantis_b200
+from frames import K_for, poses
+W, H, N = 640, 480, 200
+K, D = K_for(W, H), np.zeros(4)
+with mantis_b200.Context(0) as ctx:
+    buf = torch.empty((N, H, W, 3), dtype=torch.uint8, device="cuda:0")
+    ctx.render_grid_device(poses(N, seed=0x4D414E54 + 21), W, H, K, D, buf.data_ptr())
+    torch.cuda.synchronize()
+    frames = ctx.make_frames([buf.data_ptr() + i * H * W * 3 for i in range(N)], W, H, K, D)
+    res, tr = ctx.localize_frames(frames, mantis_b200.MEM_DEVICE, want_trace=True)
+    open(sys.argv[2], "wb").write(bytes(res) + bytes(tr))
+"""
+
+
+def test_shift_hypotheses_through_the_lattice_equal_direct_scoring(tmp_path):
+    """k_search scores the 81 cell shifts from a table of the distinct points p - shift (search.cu: score_points);
+    MANTIS_DIRECT_SHIFTS=1 projects every shift on its own, as the reference does.  Results and traces (all 81 shift
+    errors, the kept 20, yaw errors, pose) of 200 frames must be the same bytes.  (The variable is read once per
+    process, hence the two child processes.)"""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for name, extra in (("table", {}), ("direct", {"MANTIS_DIRECT_SHIFTS": "1"})):
+        path = str(tmp_path / (name + ".bin"))
+        env = {k: v for k, v in os.environ.items() if k != "MANTIS_DIRECT_SHIFTS"}
+        env.update(extra)
+        subprocess.run([sys.executable, "-c", _SHIFT_CHILD, root, path], check=True, env=env, timeout=600)
+        outs.append(open(path, "rb").read())
+    assert len(outs[0]) > 200 * 64 and outs[0] == outs[1]
