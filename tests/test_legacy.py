@@ -121,6 +121,74 @@ def test_oracle_camera_error_counts_and_floor():
     assert far == np.inf or far >= 1e15
 
 
+def _ref_montecarlo():
+    import ctypes
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libmontecarlo_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libmontecarlo_ref.so not built (reference tree absent)")
+    L = ctypes.CDLL(path)
+    vp, ci, d = ctypes.c_void_p, ctypes.c_int, ctypes.c_double
+    L.montecarlo_ref_camera_error.argtypes = [vp, ci, ci, ci, vp, vp, vp, ci, ci, ci]
+    L.montecarlo_ref_camera_error.restype = d
+    L.montecarlo_ref_weight.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, ci, ci, ci]
+    L.montecarlo_ref_weight.restype = d
+    return L
+
+
+def test_oracle_camera_error_matches_compiled_reference():
+    """oracle/legacy.c's particle weight against the reference's own MonteCarlo.cpp (project2d, colorError,
+    computeCameraError, computeWeight), compiled unmodified into oracle/_ref/libmontecarlo_ref.so (oracle/ref_build,
+    OpenCV / ROS / tf stand-ins in shim_mc): rendered frames and noise, poses around the frame's own and far off it,
+    a projection that rounds to column `cols` / row `rows`, and the fewer-than-10-points floor.  Equal doubles."""
+    L = _ref_montecarlo()
+    K, D = K_for(640, 480), np.zeros(4)
+    Kf = np.ascontiguousarray(K, np.float32)
+    w, r, g = po.make_map()
+    mp = np.ascontiguousarray(np.concatenate([w, r, g]), np.float64)
+    rng = np.random.default_rng(17)
+    frames = [po.render_grid(R, t, K, D, 640, 480) for R, t in poses(2, seed=31)]
+    frames.append(rng.integers(0, 256, (480, 640, 3), dtype=np.uint8))
+    n_checked = 0
+    for i, img in enumerate(frames):
+        img = np.ascontiguousarray(img)
+        P = list(_particles(60, 200 + i))
+        P.append(np.concatenate([np.eye(3).reshape(-1), [100, 100, 1]]))      # nothing projected: 1e17 / 0
+        P.append(np.concatenate([np.eye(3).reshape(-1), [0.0, 0.0, 1.0]]))    # a few points in frame
+        for T in P:
+            T = np.ascontiguousarray(T, np.float64)
+            ref = L.montecarlo_ref_camera_error(img.ctypes.data, 640, 480, 3 * 640, Kf.ctypes.data, T.ctypes.data, mp.ctypes.data,
+                                                len(w), len(r), len(g))
+            got = po.camera_error(img, K, T, w, r, g)
+            assert got == ref or (np.isinf(ref) and np.isinf(got)) or (np.isnan(ref) and np.isnan(got)), (i, got, ref)
+            n_checked += 1
+    # one map point whose projection rounds to x == cols and one to y == rows (Mat::at is unchecked)
+    one = np.array([[0.0, 0.0, 0.0]] * 12)
+    img = np.ascontiguousarray(frames[2])
+    for tx, ty, black in ((319.8 / 320.0, 0.0, False), (0.0, 239.7 / 320.0, True)):
+        T = np.concatenate([np.eye(3).reshape(-1), [tx, ty, 1.0]])
+        ref = L.montecarlo_ref_camera_error(img.ctypes.data, 640, 480, 3 * 640, Kf.ctypes.data, T.ctypes.data, one.ctypes.data, 12, 0, 0)
+        got = po.camera_error(img, K, T, one, one[:0], one[:0])
+        assert got == ref
+        # x == cols is the first pixel of the next row (linear addressing); y == rows lies below the image: black
+        expect = 3 * 255 ** 2 if black else int(((img[241, 0].astype(int) - 255) ** 2).sum())
+        assert got == float(expect)
+    # computeWeight: particle (world <- base) and base -> camera
+    for k, (R, t) in enumerate(poses(8, seed=77)):
+        b2c = np.concatenate([np.array([[0, -1, 0], [-1, 0, 0], [0, 0, -1.0]]).reshape(-1), [0.02, -0.01, 0.05]])
+        part = np.concatenate([R.reshape(-1), t])
+        ref = L.montecarlo_ref_weight(img.ctypes.data, 640, 480, 3 * 640, Kf.ctypes.data, part.ctypes.data, b2c.ctypes.data,
+                                      mp.ctypes.data, len(w), len(r), len(g))
+        Rp, tp, Rb, tb = R, t, b2c[:9].reshape(3, 3), b2c[9:]
+        # inverse() and the product as tf composes them: inv = (Rp^T, -Rp^T tp), b2c_inv = (Rb^T, -Rb^T tb)
+        Ri, ti = Rp.T, -(Rp.T @ tp)
+        Rbi, tbi = Rb.T, -(Rb.T @ tb)
+        T = np.concatenate([(Ri @ Rbi).reshape(-1), Ri @ tbi + ti])
+        got = po.camera_error(img, K, T, w, r, g)
+        assert got == pytest.approx(ref, rel=1e-9) or (np.isinf(ref) and np.isinf(got)), (k, got, ref)
+    assert n_checked == 3 * 62
+
+
 @pytest.mark.gpu
 def test_cuda_undistort_matches_oracle(ctx):
     for name, K in (("lena", K_LENA), ("odd_33x129", K_for(129, 33))):
