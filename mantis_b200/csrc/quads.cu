@@ -828,17 +828,50 @@ __device__ __forceinline__ int back_dir(uint32_t nb, int side)
     return (side + 31 - __clz((int)rot)) & 7;
 }
 
+// One step of walk_piece() with the walk's state in the caller's registers (the lanes of a warp are each inside a
+// different piece).  Returns true when (x, y, s) is the cut visit that ends the piece; else moves on one border pixel.
+template <class Img>
+__device__ __forceinline__ bool walk_step(const Img& im, const CutSet& cs, int& x, int& y, int& s, int& prev_s, uint32_t& nb,
+                                          bool& first, int& np, short2* tmp)
+{
+    const int r0 = (s + 1) & 7;
+    const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
+    const int k = __ffs(rot) - 1;
+    uint32_t z = ((1u << k) - 1u) << r0;
+    z = (z | (z >> 8)) & 0xffu;
+    if (!first && cs.is_cut(x, y, nb, z)) return true;
+    first = false;
+    s = (r0 + k) & 7;
+    if (s != prev_s) {
+        if (tmp && np < TMPV) tmp[np] = make_short2((short)x, (short)y);
+        ++np;
+        prev_s = s;
+    }
+    x += dir_dx(s);
+    y += dir_dy(s);
+    s = (s + 4) & 7;
+    nb = im.nbr(x, y);
+    return false;
+}
+
+// One CTA per frame.  Pieces are 1 .. 400 steps long (19 on average, measured), so with a fixed piece per lane a
+// warp waits for the longest of its 32: a third of the lanes work.  Here a lane takes the next cut of the frame
+// from a shared counter whenever it has finished its piece (checked every STEPS steps; same scheme as pose.cu's
+// k_pose_run).  The hole candidates' walks to a cut of their parent border run the same way in a second pass.
 template <bool GPAD>
 __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
 {
     __shared__ uint32_t s_tab[TABN];
-    const int frame = blockIdx.x, W = a.W;
+    __shared__ int s_next, s_npar, s_next_par;
+    __shared__ unsigned short s_par[MAXCC];   // slots whose hole needs a parent walk
+    const int frame = blockIdx.x, W = a.W, lane = threadIdx.x & 31;
     QMeta* meta = a.meta + frame;
     if (meta->fallback) return;
     const int ncut = meta->ncut;
     const size_t base = (size_t)frame * MAXCUT;
     CutSet cs{s_tab, W, a.cut_mask};
     for (int i = threadIdx.x; i < TABN; i += CNT) s_tab[i] = EMPTY;
+    if (threadIdx.x == 0) { s_next = 0; s_npar = 0; s_next_par = 0; }
     __syncthreads();
     for (int i = threadIdx.x; i < ncut; i += CNT) {
         const uint32_t raw = a.cut[base + i];
@@ -847,52 +880,135 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
     PadImg im;
     if (GPAD) { im = global_padded(a, frame); __syncthreads(); }
     else im = stage_padded(a.morph_bits + (size_t)frame * a.H * a.WW, a.H, a.WW);  // (synchronises)
-    for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
-        const uint32_t raw = a.cut[base + slot];
-        const bool east = raw & 2u;
-        const int side = east ? 0 : 4, pos = (int)(raw >> 2), y = pos / W, x = pos - y * W;
-        const uint32_t nb = im.nbr(x, y);
-        uint32_t key = KEY_DEAD, end = 0;
-        int np = 0;
-        if (!(raw & 1u) && cs.has(raw >> 1)) {
-            // a row cut that is also listed as a candidate: the candidate entry stands for it
-        } else if (nb == 0u) {  // isolated pixel: one visit, one vertex; stands under its West side
-            if (!east) {
-                key = ((uint32_t)pos << 3) | KEY_LTOP; end = (uint32_t)pos << 3; np = 1;
-                a.cut_tmp[(base + slot) * TMPV] = make_short2((short)x, (short)y);
+
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int STEPS = 8, GUARD = 1 << 22;   // steps after which a walk is given up (walk_piece's bound)
+    // ---- pass 1: the pieces ----
+    {
+        int slot = 0, x = 0, y = 0, s = 0, prev_s = 0, np = 0, steps = 0;
+        uint32_t nb = 0, key = 0;
+        bool first = true, active = false, more = true;
+        short2* tmp = nullptr;
+        for (;;) {
+            const unsigned want = __ballot_sync(FULL, !active && more);
+            if (want) {
+                const int leader = __ffs(want) - 1;
+                int first_slot = 0;
+                if (lane == leader) first_slot = atomicAdd(&s_next, __popc(want));
+                first_slot = __shfl_sync(FULL, first_slot, leader);
+                if (!active && more) {
+                    slot = first_slot + __popc(want & ((1u << lane) - 1u));
+                    if (slot >= ncut) {
+                        more = false;
+                    } else {
+                        const uint32_t raw = a.cut[base + slot];
+                        const bool east = raw & 2u;
+                        const int side = east ? 0 : 4, pos = (int)(raw >> 2);
+                        y = pos / W; x = pos - y * W;
+                        nb = im.nbr(x, y);
+                        key = KEY_DEAD;
+                        uint32_t end = 0;
+                        np = 0;
+                        if (!(raw & 1u) && cs.has(raw >> 1)) {
+                            // a row cut that is also listed as a candidate: the candidate entry stands for it
+                        } else if (nb == 0u) {  // isolated pixel: one visit, one vertex; stands under its West side
+                            if (!east) {
+                                key = ((uint32_t)pos << 3) | KEY_LTOP; end = (uint32_t)pos << 3; np = 1;
+                                a.cut_tmp[(base + slot) * TMPV] = make_short2((short)x, (short)y);
+                            }
+                        } else {
+                            s = back_dir(nb, side);
+                            const int r0 = (s + 1) & 7;
+                            const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
+                            uint32_t z = ((1u << (__ffs(rot) - 1)) - 1u) << r0;
+                            z = (z | (z >> 8)) & 0xffu;
+                            if (!(east && (z & 0x10u) && cs.cut_west(x, y, nb))) {  // else the same visit stands under its West side
+                                key = ((uint32_t)pos << 3) | (uint32_t)s;
+                                if ((z & 0x10u) && cs.cand_west(x, y, nb)) key |= KEY_LTOP;
+                                if ((z & 0x01u) && cs.cand_east(x, y, nb)) key |= KEY_RCAND;
+                                prev_s = s ^ 4; first = true; steps = 0;
+                                tmp = a.cut_tmp + (base + slot) * TMPV;
+                                active = true;
+                            }
+                        }
+                        if (!active) {
+                            a.cut_key[base + slot] = key;
+                            a.cut_end[base + slot] = end;
+                            a.cut_np[base + slot] = np;
+                        }
+                    }
+                }
             }
-        } else {
-            const int s = back_dir(nb, side), r0 = (s + 1) & 7;
-            const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
-            uint32_t z = ((1u << (__ffs(rot) - 1)) - 1u) << r0;
-            z = (z | (z >> 8)) & 0xffu;
-            if (!(east && (z & 0x10u) && cs.cut_west(x, y, nb))) {  // else the same visit stands under its West side
-                key = ((uint32_t)pos << 3) | (uint32_t)s;
-                if ((z & 0x10u) && cs.cand_west(x, y, nb)) key |= KEY_LTOP;
-                if ((z & 0x01u) && cs.cand_east(x, y, nb)) key |= KEY_RCAND;
-                SegKeep v{a.cut_tmp + (base + slot) * TMPV, 0};
-                end = walk_piece(im, cs, x, y, s, nb, v);
-                np = v.np;
+            if (!__any_sync(FULL, active || more)) break;
+#pragma unroll 1
+            for (int i = 0; i < STEPS; ++i) {
+                if (!active) continue;
+                const bool done = walk_step(im, cs, x, y, s, prev_s, nb, first, np, tmp);
+                if (!done && ++steps < GUARD) continue;
+                // EMPTY: no cut met -- k_qlink finds no such visit and hands the frame to the sequential route
+                a.cut_key[base + slot] = key;
+                a.cut_end[base + slot] = done ? (((uint32_t)(y * W + x) << 3) | (uint32_t)s) : EMPTY;
+                a.cut_np[base + slot] = np;
+                if (np > 65535) meta->fallback = 1;
+                if (key & KEY_RCAND) {
+                    const int k = atomicAdd(&s_npar, 1);
+                    if (k < MAXCC) s_par[k] = (unsigned short)slot; else meta->fallback = 1;
+                }
+                active = false;
             }
         }
-        if (key & KEY_RCAND) {
-            // RETR_CCOMP parent of the hole that would start here: the border passing the left edge of
-            // the foreground run that ends at this pixel.  Any cut visit of that border identifies it:
-            // the visit examining that left edge, or the first cut after it.
-            int xl = x;
-            while (im.at(xl - 1, y)) --xl;
-            const uint32_t nbl = im.nbr(xl, y);  // not empty: the run's right end has a neighbour above
-            const int sl = back_dir(nbl, 4), r0 = (sl + 1) & 7;
-            const uint32_t rot = ((nbl | (nbl << 8)) >> r0) & 0xffu;
-            uint32_t z = ((1u << (__ffs(rot) - 1)) - 1u) << r0;
-            z = (z | (z >> 8)) & 0xffu;
-            SegKeep v{nullptr, 0};
-            a.cut_par[base + slot] = cs.is_cut(xl, y, nbl, z) ? (((uint32_t)(y * W + xl) << 3) | (uint32_t)sl) : walk_piece(im, cs, xl, y, sl, nbl, v);
+    }
+    __syncthreads();
+    // ---- pass 2: RETR_CCOMP parent of the hole that would start at a KEY_RCAND visit: the border passing the left
+    // edge of the foreground run that ends at this pixel.  Any cut visit of that border identifies it: the visit
+    // examining that left edge, or the first cut after it. ----
+    {
+        const int npar = min(s_npar, MAXCC);
+        int slot = 0, x = 0, y = 0, s = 0, prev_s = 0, np = 0, steps = 0;
+        uint32_t nb = 0;
+        bool first = true, active = false, more = true;
+        for (;;) {
+            const unsigned want = __ballot_sync(FULL, !active && more);
+            if (want) {
+                const int leader = __ffs(want) - 1;
+                int first_item = 0;
+                if (lane == leader) first_item = atomicAdd(&s_next_par, __popc(want));
+                first_item = __shfl_sync(FULL, first_item, leader);
+                if (!active && more) {
+                    const int item = first_item + __popc(want & ((1u << lane) - 1u));
+                    if (item >= npar) {
+                        more = false;
+                    } else {
+                        slot = s_par[item];
+                        const int pos = (int)(a.cut[base + slot] >> 2);
+                        y = pos / W;
+                        x = pos - y * W;
+                        while (im.at(x - 1, y)) --x;
+                        nb = im.nbr(x, y);  // not empty: the run's right end has a neighbour above
+                        s = back_dir(nb, 4);
+                        const int r0 = (s + 1) & 7;
+                        const uint32_t rot = ((nb | (nb << 8)) >> r0) & 0xffu;
+                        uint32_t z = ((1u << (__ffs(rot) - 1)) - 1u) << r0;
+                        z = (z | (z >> 8)) & 0xffu;
+                        if (cs.is_cut(x, y, nb, z)) {
+                            a.cut_par[base + slot] = ((uint32_t)(y * W + x) << 3) | (uint32_t)s;
+                        } else {
+                            prev_s = s ^ 4; first = true; steps = 0; np = 0;
+                            active = true;
+                        }
+                    }
+                }
+            }
+            if (!__any_sync(FULL, active || more)) break;
+#pragma unroll 1
+            for (int i = 0; i < STEPS; ++i) {
+                if (!active) continue;
+                const bool done = walk_step(im, cs, x, y, s, prev_s, nb, first, np, nullptr);
+                if (!done && ++steps < GUARD) continue;
+                a.cut_par[base + slot] = done ? (((uint32_t)(y * W + x) << 3) | (uint32_t)s) : EMPTY;
+                active = false;
+            }
         }
-        if (np > 65535) meta->fallback = 1;
-        a.cut_key[base + slot] = key;
-        a.cut_end[base + slot] = end;
-        a.cut_np[base + slot] = np;
     }
 }
 
