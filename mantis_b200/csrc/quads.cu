@@ -383,7 +383,7 @@ struct QMeta {  // per frame, zeroed before every batch
     int ncand, nstart, flags, nb, nlong, ncut, fallback, ncc;
 };
 constexpr int LONG_NP = 96;   // contours with more vertices are handled by a whole warp
-constexpr int TMPV = 32;      // vertices of a piece that the first walk keeps; a piece with more is walked again by k_qemit
+constexpr int TMPV = 64;      // vertices of a piece that the first walk keeps; a piece with more is walked again by k_qemit
 constexpr int MAXLONG = MANTIS_MAX_PTS / LONG_NP + 1;
 
 struct QuadArgs {
@@ -887,9 +887,21 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
     {
         int slot = 0, x = 0, y = 0, s = 0, prev_s = 0, np = 0, steps = 0;
         uint32_t nb = 0, key = 0;
-        bool first = true, active = false, more = true;
+        bool first = true, active = false, more = true, finished = false;
+        uint32_t end_key = 0;
         short2* tmp = nullptr;
         for (;;) {
+            if (finished) {   // results of the piece that ended during the last STEPS steps (kept out of the step loop)
+                a.cut_key[base + slot] = key;
+                a.cut_end[base + slot] = end_key;
+                a.cut_np[base + slot] = np;
+                if (np > 65535) meta->fallback = 1;
+                if (key & KEY_RCAND) {
+                    const int k = atomicAdd(&s_npar, 1);
+                    if (k < MAXCC) s_par[k] = (unsigned short)slot; else meta->fallback = 1;
+                }
+                finished = false;
+            }
             const unsigned want = __ballot_sync(FULL, !active && more);
             if (want) {
                 const int leader = __ffs(want) - 1;
@@ -946,15 +958,9 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
                 const bool done = walk_step(im, cs, x, y, s, prev_s, nb, first, np, tmp);
                 if (!done && ++steps < GUARD) continue;
                 // EMPTY: no cut met -- k_qlink finds no such visit and hands the frame to the sequential route
-                a.cut_key[base + slot] = key;
-                a.cut_end[base + slot] = done ? (((uint32_t)(y * W + x) << 3) | (uint32_t)s) : EMPTY;
-                a.cut_np[base + slot] = np;
-                if (np > 65535) meta->fallback = 1;
-                if (key & KEY_RCAND) {
-                    const int k = atomicAdd(&s_npar, 1);
-                    if (k < MAXCC) s_par[k] = (unsigned short)slot; else meta->fallback = 1;
-                }
+                end_key = done ? (((uint32_t)(y * W + x) << 3) | (uint32_t)s) : EMPTY;
                 active = false;
+                finished = true;
             }
         }
     }
@@ -966,8 +972,10 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
         const int npar = min(s_npar, MAXCC);
         int slot = 0, x = 0, y = 0, s = 0, prev_s = 0, np = 0, steps = 0;
         uint32_t nb = 0;
-        bool first = true, active = false, more = true;
+        bool first = true, active = false, more = true, finished = false;
+        uint32_t end_key = 0;
         for (;;) {
+            if (finished) { a.cut_par[base + slot] = end_key; finished = false; }
             const unsigned want = __ballot_sync(FULL, !active && more);
             if (want) {
                 const int leader = __ffs(want) - 1;
@@ -1005,8 +1013,9 @@ __global__ void __launch_bounds__(CNT) k_qseg(QuadArgs a)
                 if (!active) continue;
                 const bool done = walk_step(im, cs, x, y, s, prev_s, nb, first, np, nullptr);
                 if (!done && ++steps < GUARD) continue;
-                a.cut_par[base + slot] = done ? (((uint32_t)(y * W + x) << 3) | (uint32_t)s) : EMPTY;
+                end_key = done ? (((uint32_t)(y * W + x) << 3) | (uint32_t)s) : EMPTY;
                 active = false;
+                finished = true;
             }
         }
     }
