@@ -381,6 +381,7 @@ __device__ int approx_poly_closed_warp(const short2* src, int count, double eps,
 
 struct QMeta {  // per frame, zeroed before every batch
     int ncand, nstart, flags, nb, nlong, ncut, fallback, ncc;
+    int rewalk, pad_[3];   // rewalk: a piece has more than TMPV vertices (k_qemit_copy -> k_qemit)
 };
 constexpr int LONG_NP = 96;   // contours with more vertices are handled by a whole warp
 constexpr int TMPV = 64;      // vertices of a piece that the first walk keeps; a piece with more is walked again by k_qemit
@@ -1129,28 +1130,49 @@ __global__ void __launch_bounds__(LNT) k_qlink(QuadArgs a)
         if (s_key[s_start[n]] & KEY_RCAND) a.hole_owner[bbase + s_rank[n]] = (short)(a.cut_dst[base + s_par[n]] & 1023u);
 }
 
-// Vertices to their place in the frame's vertex array: a copy of what k_qseg kept for pieces of up to TMPV
-// vertices; a longer piece is walked again (the frame's plane and cut table are only staged if there is one).
+// Vertices to their place in the frame's vertex array.  k_qemit_copy: what k_qseg kept for pieces of up to TMPV
+// vertices (all but a handful): no shared memory, so eight CTAs per SM wait on the loads instead of four, and the
+// first eight vertices of a piece travel as two 16-byte loads issued together (the kernel is nothing but memory
+// latency).  A frame with a longer piece is flagged and k_qemit walks those pieces again.
+__global__ void __launch_bounds__(CNT) k_qemit_copy(QuadArgs a)
+{
+    const int frame = blockIdx.x;
+    QMeta* meta = a.meta + frame;
+    if (meta->fallback || meta->flags || meta->nb == 0) return;
+    const int ncut = meta->ncut;
+    const size_t base = (size_t)frame * MAXCUT;
+    for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
+        const uint32_t d = a.cut_dst[base + slot];
+        const int np = a.cut_np[base + slot];
+        if (d == EMPTY) continue;
+        if (np > TMPV) { meta->rewalk = 1; continue; }
+        const uint4* src = reinterpret_cast<const uint4*>(a.cut_tmp + (base + slot) * TMPV);   // 256-byte aligned
+        uint32_t* dst = reinterpret_cast<uint32_t*>(a.pts + (size_t)frame * MANTIS_MAX_PTS + (d >> 10));
+        uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0;
+        if (np > 0) v0 = src[0];
+        if (np > 4) v1 = src[1];
+        if (np > 0) dst[0] = v0.x;
+        if (np > 1) dst[1] = v0.y;
+        if (np > 2) dst[2] = v0.z;
+        if (np > 3) dst[3] = v0.w;
+        if (np > 4) dst[4] = v1.x;
+        if (np > 5) dst[5] = v1.y;
+        if (np > 6) dst[6] = v1.z;
+        if (np > 7) dst[7] = v1.w;
+        const uint32_t* s1 = reinterpret_cast<const uint32_t*>(src);
+        for (int k = 8; k < np; ++k) dst[k] = s1[k];
+    }
+}
+
 template <bool GPAD>
 __global__ void __launch_bounds__(CNT) k_qemit(QuadArgs a)
 {
     __shared__ uint32_t s_tab[TABN];
     const int frame = blockIdx.x, W = a.W;
     const QMeta* meta = a.meta + frame;
-    if (meta->fallback || meta->flags || meta->nb == 0) return;
+    if (meta->fallback || meta->flags || meta->nb == 0 || !meta->rewalk) return;
     const int ncut = meta->ncut;
     const size_t base = (size_t)frame * MAXCUT;
-    int any_long = 0;
-    for (int slot = threadIdx.x; slot < ncut; slot += CNT) {
-        const uint32_t d = a.cut_dst[base + slot];
-        if (d == EMPTY) continue;
-        const int np = a.cut_np[base + slot];
-        if (np > TMPV) { any_long = 1; continue; }
-        const short2* src = a.cut_tmp + (base + slot) * TMPV;
-        short2* dst = a.pts + (size_t)frame * MANTIS_MAX_PTS + (d >> 10);
-        for (int k = 0; k < np; ++k) dst[k] = src[k];
-    }
-    if (!__syncthreads_or(any_long)) return;
     CutSet cs{s_tab, W, a.cut_mask};
     for (int i = threadIdx.x; i < TABN; i += CNT) s_tab[i] = EMPTY;
     __syncthreads();
@@ -1444,9 +1466,10 @@ int launch_quads(mantis_ctx* c, const uint32_t* d_morph_bits, int n, int w, int 
     k_qrank<<<n, CNT, 0, c->stream>>>(a);
     k_qtrace<<<n, TNT, use_smem == 1 ? plane : 0, c->stream>>>(a, use_smem);
     if (a.use_cuts) {
+        k_qemit_copy<<<n, CNT, 0, c->stream>>>(a);
         if (use_smem == 1) k_qemit<false><<<n, CNT, plane, c->stream>>>(a);
         else k_qemit<true><<<n, CNT, 0, c->stream>>>(a);
-        c->launches += 1;
+        c->launches += 2;
     }
     k_qapprox_long<<<n, 32 * LWARPS, 0, c->stream>>>(a);
     k_qfinish<<<n, FNT, 0, c->stream>>>(a);
