@@ -5,7 +5,7 @@
 //   PoseClusterer::clusterByAngle / BFcluster / keepLargestCluster / convert2Hypotheses
 //                                          PoseClusterer.cpp:33-116, PoseClusterer.h:59-115
 // RPP (rpp.cuh, rpp_fast.cuh) runs as a queue of independent ObjPose runs over all quads of the
-// batch (k_pose_run), for up to two corner orderings; passing quads emit four
+// batch (k_pose_run) for corner ordering 0; ordering 1 is its mirror (k_pose_prep); passing quads emit four
 // yaw-rotated hypotheses in quad order.  The greedy Euler-space clustering is sequential over
 // seeds (as in the reference) and parallel over members.
 #include <stdlib.h>

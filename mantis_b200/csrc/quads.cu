@@ -703,10 +703,11 @@ __global__ void __launch_bounds__(TNT) k_qtrace(QuadArgs a, int use_smem)
 //               candidate's kind says whether the cycle is an outer or a hole border,
 //   rows        every visit examining West or East on the rows y % CUT_ROWS == 0 (bounds the pieces).
 //   k_qcut   lists the cut visits of a frame, bit-parallel.
-//   k_qseg   one thread per cut: walks to the next cut, counting CHAIN_APPROX_SIMPLE vertices.
+//   k_qseg   walks every piece to the next cut (lanes take pieces from a shared counter), counting its
+//            CHAIN_APPROX_SIMPLE vertices and keeping the first TMPV of them.
 //   k_qlink  per frame: links the pieces into cycles (hash of visit keys), finds every cycle's
 //            start, ranks the starts in discovery order, gives every piece its place in the vertex array.
-//   k_qemit  one thread per cut: second walk, writing vertices and left-edge owners.
+//   k_qemit_copy  puts the kept vertices at their place; k_qemit walks the few pieces with more than TMPV again.
 // approxPolyDP then runs per border (k_qapprox_long).  A frame that exceeds MAXCUT / MAXCC, or whose
 // links do not close, is handed to the sequential-walk kernels above (meta->fallback).
 constexpr int CUT_ROWS = 16;
