@@ -256,7 +256,7 @@ def _map_struct(maps=None):
         w, r, g = maps if maps is not None else make_map()
         w, r, g = (np.ascontiguousarray(a, np.float64) for a in (w, r, g))
         m = _Map(len(w), len(r), len(g), w.ctypes.data, r.ctypes.data, g.ctypes.data)
-        _MAP_KEEP[key] = (m, w, r, g)
+        _MAP_KEEP[key] = (m, w, r, g, maps)   # (holding `maps` keeps its id from being handed to another tuple)
     return _MAP_KEEP[key][0]
 
 
